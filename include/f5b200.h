@@ -1,0 +1,119 @@
+/* libf5b200 -- C ABI of the B200-native CFM.sample + Vocos hot path.
+ *
+ * The reference (KwangsungKim138/Korean-F5-TTS, a fork of SWivid/F5-TTS 1.1.15) has no FFI/plugin interface: its
+ * "operator API" for this path is Python.  Each entry point below replaces the body of one reference
+ * Python callable; the Python mirror in korean-f5-tts_b200/f5b200/ keeps the reference signatures and binds these
+ * symbols with ctypes (INTEGRATION.md shows the stub a reference maintainer would add).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; tensors are dense row-major fp32 unless stated; `text` is int64 with -1 padding.
+ *   - `mem` says where the data pointers live: F5B_MEM_HOST (the library stages H2D/D2H itself, pinned staging is the
+ *     caller's business) or F5B_MEM_DEVICE (pointers on the plan's CUDA device).  `stream` is a cudaStream_t (may be 0).
+ *   - every function returns 0 or a negative F5B_ERR_* code; f5b_last_error() gives the thread-local message.
+ *   - there is NO CPU fallback: without an sm_100 device every compute entry returns F5B_ERR_NO_DEVICE.
+ */
+#ifndef F5B200_H_
+#define F5B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define F5B_OK 0
+#define F5B_ERR_INVALID (-1)
+#define F5B_ERR_CUDA (-2)
+#define F5B_ERR_NO_DEVICE (-3)
+#define F5B_ERR_MISSING (-4)
+
+#define F5B_MEM_HOST 0
+#define F5B_MEM_DEVICE 1
+
+#define F5B_MODE_FP32 0 /* CUDA-core fp32 contractions: parity mode (mel/wave max-abs 1e-3 vs the fp32 reference) */
+#define F5B_MODE_BF16 1 /* tcgen05 bf16 contractions, fp32 accumulate / residual / ODE state: performance mode */
+
+#define F5B_BACKBONE_DIT 0   /* reference src/f5_tts/model/backbones/dit.py:146-329 */
+#define F5B_BACKBONE_UNETT 1 /* reference src/f5_tts/model/backbones/unett.py:107-280 */
+
+/* Constructor arguments of DiT (dit.py:147-168) / UNetT (unett.py:108-127) that change the arithmetic. */
+typedef struct f5b_arch {
+  int32_t backbone;
+  int32_t dim, depth, heads, dim_head, ff_mult, mel_dim;
+  int32_t text_num_embeds; /* as passed to the constructor; the embedding table has text_num_embeds + 1 rows */
+  int32_t text_dim, conv_layers;
+  int32_t text_mask_padding;
+  int32_t pe_attn_head; /* number of leading heads that get RoPE; <= 0 means all (None in the reference) */
+  int32_t attn_mask_enabled;
+} f5b_arch;
+
+/* One state-dict entry (names exactly as the reference registers them, without the "transformer." prefix). */
+typedef struct f5b_tensor {
+  const char* name;
+  const float* data; /* fp32, contiguous */
+  int64_t numel;
+  int32_t on_device; /* 0: host pointer, 1: device pointer */
+} f5b_tensor;
+
+typedef struct f5b_plan f5b_plan;   /* backbone weights + workspace + CUDA graphs (one per shape key) */
+typedef struct f5b_vocos f5b_vocos; /* Vocos weights + workspace */
+
+const char* f5b_last_error(void);
+int f5b_version(void);
+/* 0 if an sm_100 device is usable, F5B_ERR_NO_DEVICE otherwise (message says why). */
+int f5b_device_check(int device);
+
+/* Replaces: DiT.__init__/UNetT.__init__ + load_state_dict placement on device (infer/utils_infer.py:292-345). */
+int f5b_plan_create(const f5b_arch* arch, const f5b_tensor* weights, int32_t n_weights, int32_t mode, int32_t device,
+                    f5b_plan** out);
+void f5b_plan_destroy(f5b_plan* plan);
+
+/* Replaces the ODE part of CFM.sample (model/cfm.py:160-219): text-embedding cache, EPSS/sway grid consumption,
+ * CFG-doubled backbone evaluations, Euler updates.  Inputs are what cfm.py:104-216 builds on the host:
+ *   y0        [B, N, mel]   seeded noise (cfm.py:196-201)
+ *   step_cond [B, N, mel]   where(cond_mask, cond, 0) (cfm.py:151-153)
+ *   text      [B, nt] int64 token ids, -1 padded (model/utils.py:99-106)
+ *   durations [B] int32 or NULL.  NULL <=> the reference's mask=None (batch 1, cfm.py:155-158)
+ *   t_grid    [steps+1] HOST floats, already sway-warped (cfm.py:211-216)
+ * Outputs: y_out [B, N, mel] = trajectory[-1]; traj [steps+1, B, N, mel] or NULL. */
+int f5b_sample(f5b_plan* plan, const float* y0, const float* step_cond, const int64_t* text, const int32_t* durations,
+               int32_t B, int32_t N, int32_t nt, const float* t_grid, int32_t steps, float cfg_strength, float* y_out,
+               float* traj, int32_t mem, void* stream);
+
+/* Replaces DiT.forward / UNetT.forward (dit.py:278-329, unett.py:217-280): one function evaluation.
+ *   x, cond [B, N, mel]; time [B] HOST floats; durations as above; out [(cfg_infer ? 2B : B), N, mel].
+ *   cache != 0 keeps the text embeddings until f5b_clear_cache (dit.py:259-276). */
+int f5b_forward(f5b_plan* plan, const float* x, const float* cond, const int64_t* text, const float* time,
+                const int32_t* durations, int32_t B, int32_t N, int32_t nt, int32_t drop_audio_cond, int32_t drop_text,
+                int32_t cfg_infer, int32_t cache, float* out, int32_t mem, void* stream);
+int f5b_clear_cache(f5b_plan* plan);
+
+/* Replaces MelSpec.forward (model/modules.py:78-104,133-146): wav [B, nw] -> mel [B, 100, nw/256 + 1]. */
+int f5b_mel(const float* wav, int32_t B, int32_t nw, float* mel, int32_t device, int32_t mem, void* stream);
+
+/* Replaces load_vocoder("vocos") + Vocos.decode (infer/utils_infer.py:114-137,703): mel [B,100,T] -> wav [B,(T-1)*256]. */
+int f5b_vocos_create(const f5b_tensor* weights, int32_t n_weights, int32_t mode, int32_t device, f5b_vocos** out);
+void f5b_vocos_destroy(f5b_vocos* v);
+int f5b_vocos_decode(f5b_vocos* v, const float* mel, int32_t B, int32_t T, float* wav, int32_t mem, void* stream);
+
+/* Kernel-level entry points used by the parity tests and the roofline benchmark (device pointers only).
+ *   gemm:      out[M,N] = act(A[M,K] W[N,K]^T + bias); mode selects fp32 SIMT or bf16 tcgen05 (inputs fp32, converted)
+ *   attention: qkv [batches*rows, 3*heads*64] fp32 -> out [batches*rows, heads*64] fp32 */
+int f5b_op_gemm(int32_t mode, const float* A, const float* W, const float* bias, int32_t M, int32_t N, int32_t K,
+                int32_t act, float* out, int32_t force_bn, int32_t device, void* stream);
+int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int32_t batches, int32_t rows,
+                     int32_t heads, float* out, int32_t device, void* stream);
+/* Times `iters` back-to-back launches of one kernel with CUDA events on `stream`; returns average ms in *ms.
+ *   which: 0 = bf16 tcgen05 GEMM [M,K]x[N,K], 1 = bf16 tcgen05 attention (M = rows, N = heads, K = batches),
+ *          2 = LN+modulate (M rows, N = dim). */
+int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, float* ms, int32_t device, void* stream);
+
+/* Number of kernel launches issued by this library since load (for bench.py's gpu_launches). */
+int64_t f5b_launch_count(void);
+/* Kernel launches inside the last f5b_sample / f5b_vocos_decode / f5b_mel call (graph nodes count individually). */
+int64_t f5b_last_call_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* F5B200_H_ */

@@ -1,0 +1,493 @@
+// Memory-bound kernels of the CFM.sample path: fused, coalesced, 128-bit vectorised, warp-shuffle reductions.
+// One warp owns one row wherever a row statistic is needed (rows are 2-4 KB: the re-reads hit L1).
+#include "rowwise.h"
+
+namespace f5b {
+
+static inline int ceil_div_ll(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+template <typename T>
+__device__ __forceinline__ void store4(T* p, float a, float b, float c, float d);
+template <>
+__device__ __forceinline__ void store4<float>(float* p, float a, float b, float c, float d) {
+  *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+template <>
+__device__ __forceinline__ void store4<bf16>(bf16* p, float a, float b, float c, float d) {
+  uint2 pk;
+  pk.x = pack_bf16x2(a, b);
+  pk.y = pack_bf16x2(c, d);
+  *reinterpret_cast<uint2*>(p) = pk;
+}
+template <typename T>
+__device__ __forceinline__ float4 load4(const T* p);
+template <>
+__device__ __forceinline__ float4 load4<float>(const float* p) {
+  return *reinterpret_cast<const float4*>(p);
+}
+template <>
+__device__ __forceinline__ float4 load4<bf16>(const bf16* p) {
+  uint2 r = *reinterpret_cast<const uint2*>(p);
+  __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&r.x);
+  __nv_bfloat162 b = *reinterpret_cast<__nv_bfloat162*>(&r.y);
+  float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+  return make_float4(fa.x, fa.y, fb.x, fb.y);
+}
+
+// ---------------------------------------------------------------------------------------------
+// LayerNorm (no affine) + modulation / affine
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+ln_mod_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d, const float* __restrict__ mul,
+              const float* __restrict__ add, float mul_off, long long vec_bstride, int rows_per_batch, int bmod,
+              float eps) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= M) return;
+  const float* xr = x + m * d;
+  float s = 0.0f;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(xr + c);
+    s += (v.x + v.y) + (v.z + v.w);
+  }
+  const float mean = warp_sum(s) / d;
+  float q = 0.0f;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(xr + c);
+    float a = v.x - mean, b = v.y - mean, cc = v.z - mean, dd = v.w - mean;
+    q += (a * a + b * b) + (cc * cc + dd * dd);
+  }
+  const float rstd = rsqrtf(warp_sum(q) / d + eps);
+  const int b = (int)((m / rows_per_batch) % bmod);
+  const float* mu = mul ? mul + b * vec_bstride : nullptr;
+  const float* ad = add ? add + b * vec_bstride : nullptr;
+  T* orow = out + m * d;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(xr + c);
+    float4 g = mu ? __ldg(reinterpret_cast<const float4*>(mu + c)) : make_float4(0, 0, 0, 0);
+    float4 h = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
+    if (!mu) g = make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
+    store4<T>(orow + c, (v.x - mean) * rstd * (mul_off + g.x) + h.x, (v.y - mean) * rstd * (mul_off + g.y) + h.y,
+              (v.z - mean) * rstd * (mul_off + g.z) + h.z, (v.w - mean) * rstd * (mul_off + g.w) + h.w);
+  }
+}
+
+template <typename T>
+void ln_mod(cudaStream_t st, const float* x, T* out, long long M, int d, const float* mul, const float* add,
+            float mul_off, long long vec_bstride, int rows_per_batch, int bmod, float eps) {
+  F5B_REQUIRE(d % 4 == 0, "LayerNorm width must be a multiple of 4");
+  ln_mod_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride, rows_per_batch,
+                                                      bmod < 1 ? 1 : bmod, eps);
+  F5B_POST_LAUNCH();
+}
+template void ln_mod<float>(cudaStream_t, const float*, float*, long long, int, const float*, const float*, float,
+                            long long, int, int, float);
+template void ln_mod<bf16>(cudaStream_t, const float*, bf16*, long long, int, const float*, const float*, float,
+                           long long, int, int, float);
+
+// ---------------------------------------------------------------------------------------------
+// x_transformers RMSNorm
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+xrms_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d, const float* __restrict__ g,
+            float sqrt_d) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= M) return;
+  const float* xr = x + m * d;
+  float q = 0.0f;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(xr + c);
+    q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+  }
+  const float nrm = fmaxf(sqrtf(warp_sum(q)), 1e-12f);
+  const float sc = sqrt_d / nrm;
+  T* orow = out + m * d;
+  for (int c = lane * 4; c < d; c += 128) {
+    float4 v = *reinterpret_cast<const float4*>(xr + c);
+    float4 gg = __ldg(reinterpret_cast<const float4*>(g + c));
+    store4<T>(orow + c, v.x * sc * gg.x, v.y * sc * gg.y, v.z * sc * gg.z, v.w * sc * gg.w);
+  }
+}
+template <typename T>
+void xrms_norm(cudaStream_t st, const float* x, T* out, long long M, int d, const float* g) {
+  F5B_REQUIRE(d % 4 == 0, "RMSNorm width must be a multiple of 4");
+  xrms_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, g, sqrtf((float)d));
+  F5B_POST_LAUNCH();
+}
+template void xrms_norm<float>(cudaStream_t, const float*, float*, long long, int, const float*);
+template void xrms_norm<bf16>(cudaStream_t, const float*, bf16*, long long, int, const float*);
+
+// ---------------------------------------------------------------------------------------------
+// depthwise conv k7 + bias + LayerNorm(affine): one warp per output row, <= 32 channels per lane
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+dwconv7_ln_kernel(const float* __restrict__ x, T* __restrict__ out, int batches, int rows, int d,
+                  const int* __restrict__ row_len, const float* __restrict__ w_t, const float* __restrict__ bias,
+                  const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= (long long)batches * rows) return;
+  const int b = (int)(m / rows), pos = (int)(m - (long long)b * rows);
+  const int len = row_len ? row_len[b] : rows;
+  const float* xb = x + (long long)b * rows * d;
+  float acc[32];
+  float s = 0.0f;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int c = lane * 4 + it * 128;
+    float4 a = make_float4(0, 0, 0, 0);
+    if (c < d) {
+      a = __ldg(reinterpret_cast<const float4*>(bias + c));
+#pragma unroll
+      for (int k = 0; k < 7; ++k) {
+        int p = pos + k - 3;
+        if (p >= 0 && p < len) {
+          float4 v = *reinterpret_cast<const float4*>(xb + (long long)p * d + c);
+          float4 w = __ldg(reinterpret_cast<const float4*>(w_t + k * d + c));
+          a.x = fmaf(v.x, w.x, a.x); a.y = fmaf(v.y, w.y, a.y); a.z = fmaf(v.z, w.z, a.z); a.w = fmaf(v.w, w.w, a.w);
+        }
+      }
+      s += (a.x + a.y) + (a.z + a.w);
+    }
+    acc[it * 4] = a.x; acc[it * 4 + 1] = a.y; acc[it * 4 + 2] = a.z; acc[it * 4 + 3] = a.w;
+  }
+  const float mean = warp_sum(s) / d;
+  float q = 0.0f;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    if (lane * 4 + it * 128 < d) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float t = acc[it * 4 + j] - mean;
+        q += t * t;
+      }
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / d + eps);
+  T* orow = out + m * d;
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int c = lane * 4 + it * 128;
+    if (c < d) {
+      const int i = it * 4;
+      float4 w = __ldg(reinterpret_cast<const float4*>(ln_w + c));
+      float4 bb = __ldg(reinterpret_cast<const float4*>(ln_b + c));
+      store4<T>(orow + c, (acc[i] - mean) * rstd * w.x + bb.x, (acc[i + 1] - mean) * rstd * w.y + bb.y,
+                (acc[i + 2] - mean) * rstd * w.z + bb.z, (acc[i + 3] - mean) * rstd * w.w + bb.w);
+    }
+  }
+}
+template <typename T>
+void dwconv7_ln(cudaStream_t st, const float* x, T* out, int batches, int rows, int d, const int* row_len,
+                const float* w_t, const float* bias, const float* ln_w, const float* ln_b, float eps) {
+  F5B_REQUIRE(d % 4 == 0 && d <= 1024, "depthwise conv width must be a multiple of 4, <= 1024");
+  dwconv7_ln_kernel<T><<<ceil_div_ll((long long)batches * rows, 8), 256, 0, st>>>(x, out, batches, rows, d, row_len,
+                                                                                 w_t, bias, ln_w, ln_b, eps);
+  F5B_POST_LAUNCH();
+}
+template void dwconv7_ln<float>(cudaStream_t, const float*, float*, int, int, int, const int*, const float*,
+                                const float*, const float*, const float*, float);
+template void dwconv7_ln<bf16>(cudaStream_t, const float*, bf16*, int, int, int, const int*, const float*,
+                               const float*, const float*, const float*, float);
+
+// ---------------------------------------------------------------------------------------------
+// GRN: gx[b,c] = ||h[b,:len,c]||_2 ; nx = gx / (mean_c gx + 1e-6) ; h = gamma*(h*nx) + beta + h
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+grn_sumsq_kernel(const T* __restrict__ h, int rows, int C, const int* __restrict__ row_len, float* __restrict__ gx) {
+  // block = (32-channel slab, batch); 8 row lanes x 32 channels, deterministic tree over the 8 row lanes
+  __shared__ float part[8][33];
+  const int b = blockIdx.y, c = blockIdx.x * 32 + (threadIdx.x & 31), rl = threadIdx.x >> 5;
+  const int len = row_len ? row_len[b] : rows;
+  float s = 0.0f;
+  if (c < C) {
+    const T* hb = h + (long long)b * rows * C + c;
+    for (int r = rl; r < len; r += 8) {
+      float v = ld_as_float(hb + (long long)r * C);
+      s = fmaf(v, v, s);
+    }
+  }
+  part[rl][threadIdx.x & 31] = s;
+  __syncthreads();
+  if (rl == 0 && c < C) {
+    float t = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += part[i][threadIdx.x];
+    gx[(long long)b * 2 * C + c] = sqrtf(t);
+  }
+}
+__global__ void __launch_bounds__(256) grn_nx_kernel(float* __restrict__ gx, int C) {
+  __shared__ float red[8];
+  float* g = gx + (long long)blockIdx.x * 2 * C;
+  float s = 0.0f;
+  for (int c = threadIdx.x; c < C; c += 256) s += g[c];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  float tot = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) tot += red[i];
+  const float denom = tot / C + 1e-6f;
+  for (int c = threadIdx.x; c < C; c += 256) g[C + c] = g[c] / denom;
+}
+template <typename T>
+__global__ void __launch_bounds__(256)
+grn_apply_kernel(T* __restrict__ h, int rows, int C, const float* __restrict__ gx, const float* __restrict__ gamma,
+                 const float* __restrict__ beta, long long total4) {
+  const long long i4 = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i4 >= total4) return;
+  const long long e = i4 * 4;
+  const int c = (int)(e % C);
+  const int b = (int)(e / ((long long)rows * C));
+  const float* nx = gx + (long long)b * 2 * C + C + c;
+  float4 v = load4<T>(h + e);
+  float4 g = __ldg(reinterpret_cast<const float4*>(gamma + c));
+  float4 bt = __ldg(reinterpret_cast<const float4*>(beta + c));
+  float4 n = *reinterpret_cast<const float4*>(nx);
+  store4<T>(h + e, g.x * (v.x * n.x) + bt.x + v.x, g.y * (v.y * n.y) + bt.y + v.y, g.z * (v.z * n.z) + bt.z + v.z,
+            g.w * (v.w * n.w) + bt.w + v.w);
+}
+template <typename T>
+void grn_inplace(cudaStream_t st, T* h, int batches, int rows, int C, const int* row_len, const float* gamma,
+                 const float* beta, float* scratch) {
+  F5B_REQUIRE(C % 4 == 0, "GRN width must be a multiple of 4");
+  grn_sumsq_kernel<T><<<dim3((C + 31) / 32, batches), 256, 0, st>>>(h, rows, C, row_len, scratch);
+  grn_nx_kernel<<<batches, 256, 0, st>>>(scratch, C);
+  long long total4 = (long long)batches * rows * C / 4;
+  grn_apply_kernel<T><<<ceil_div_ll(total4, 256), 256, 0, st>>>(h, rows, C, scratch, gamma, beta, total4);
+  F5B_POST_LAUNCH();
+}
+template void grn_inplace<float>(cudaStream_t, float*, int, int, int, const int*, const float*, const float*, float*);
+template void grn_inplace<bf16>(cudaStream_t, bf16*, int, int, int, const int*, const float*, const float*, float*);
+
+// ---------------------------------------------------------------------------------------------
+// text token lookup (+ sinus position table, + padding mask); one warp per (batch, position)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+text_lookup_kernel(const long long* __restrict__ text, int B, int nt, int uncond_from, int batches, int rows, int td,
+                   const int* __restrict__ row_len, const float* __restrict__ table,
+                   const float* __restrict__ inv_freq, int mask_padding, float* __restrict__ out,
+                   unsigned char* __restrict__ keep) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= (long long)batches * rows) return;
+  const int b2 = (int)(m / rows), pos = (int)(m - (long long)b2 * rows);
+  const int b = b2 % B;
+  const int len = row_len ? row_len[b2] : rows;
+  long long tok = 0;
+  if (pos < nt && pos < len) tok = text[(long long)b * nt + pos] + 1;
+  const bool is_pad = tok == 0;
+  if (b2 >= uncond_from) tok = 0;
+  const bool exists = pos < len;
+  const bool kp = exists && !(mask_padding && is_pad);
+  if (lane == 0 && keep) keep[m] = kp ? 1 : 0;
+  const float* e = table + tok * td;
+  float* o = out + m * td;
+  const int half = td / 2;
+  for (int c = lane; c < td; c += 32) {
+    float v = 0.0f;
+    if (exists) {
+      v = e[c];
+      if (inv_freq) {
+        float ang = (float)pos * inv_freq[c < half ? c : c - half];
+        v += c < half ? cosf(ang) : sinf(ang);
+        if (mask_padding && is_pad) v = 0.0f;
+      }
+    }
+    o[c] = v;
+  }
+}
+void text_lookup(cudaStream_t st, const long long* text, int B, int nt, int branches_uncond_from, int batches,
+                 int rows, int td, const int* row_len, const float* table, const float* inv_freq, int mask_padding,
+                 float* out, unsigned char* keep) {
+  text_lookup_kernel<<<ceil_div_ll((long long)batches * rows, 8), 256, 0, st>>>(
+      text, B, nt, branches_uncond_from, batches, rows, td, row_len, table, inv_freq, mask_padding, out, keep);
+  F5B_POST_LAUNCH();
+}
+
+__global__ void __launch_bounds__(256)
+mask_rows_kernel(float* __restrict__ x, long long total4, int d4, const unsigned char* __restrict__ keep) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total4) return;
+  if (!keep[i / d4]) reinterpret_cast<float4*>(x)[i] = make_float4(0, 0, 0, 0);
+}
+void mask_rows(cudaStream_t st, float* x, long long M, int d, const unsigned char* keep) {
+  long long total4 = M * d / 4;
+  mask_rows_kernel<<<ceil_div_ll(total4, 256), 256, 0, st>>>(x, total4, d / 4, keep);
+  F5B_POST_LAUNCH();
+}
+
+// ---------------------------------------------------------------------------------------------
+// sampler glue: A_in assembly, CFG combine + Euler update, masks, tables
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+build_a_in_kernel(T* __restrict__ a_in, long long ld, int B, int batches, int rows, int mel, int td,
+                  const float* __restrict__ cond, const float* __restrict__ text_emb, int uncond_from) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= (long long)batches * rows) return;
+  const int b2 = (int)(m / rows), pos = (int)(m - (long long)b2 * rows);
+  const int b = b2 % B;
+  T* row = a_in + m * ld;
+  const float* cr = cond + ((long long)b * rows + pos) * mel;
+  const bool drop = b2 >= uncond_from;
+  for (int c = lane; c < mel; c += 32) st_from_float(row + mel + c, drop ? 0.0f : cr[c]);
+  const float* tr = text_emb + m * td;
+  for (int c = lane; c < td; c += 32) st_from_float(row + 2 * mel + c, tr[c]);
+}
+template <typename T>
+void build_a_in(cudaStream_t st, T* a_in, long long ld, int B, int batches, int rows, int mel, int td,
+                const float* cond, const float* text_emb, int uncond_from) {
+  build_a_in_kernel<T><<<ceil_div_ll((long long)batches * rows, 8), 256, 0, st>>>(a_in, ld, B, batches, rows, mel, td,
+                                                                                 cond, text_emb, uncond_from);
+  F5B_POST_LAUNCH();
+}
+template void build_a_in<float>(cudaStream_t, float*, long long, int, int, int, int, int, const float*, const float*, int);
+template void build_a_in<bf16>(cudaStream_t, bf16*, long long, int, int, int, int, int, const float*, const float*, int);
+
+// v [branches*B*rows, mel]: branch 0 = cond prediction, branch 1 = uncond.  dt == 0 with v == null just scatters y.
+template <typename T>
+__global__ void __launch_bounds__(256)
+cfg_euler_kernel(float* __restrict__ y, const float* __restrict__ v, T* __restrict__ a_in, long long ld, int B,
+                 int branches, int rows, int mel, float dt, float cfg, float* __restrict__ traj, long long total) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  const long long m = i / mel;
+  const int c = (int)(i - m * mel);
+  float yv = y[i];
+  if (v != nullptr) {
+    float pc = v[i];
+    float vel = pc;
+    if (branches == 2) {
+      float pu = v[total + i];
+      vel = pc + (pc - pu) * cfg;
+    }
+    yv = yv + dt * vel;
+    y[i] = yv;
+  }
+  if (traj) traj[i] = yv;
+  st_from_float(a_in + m * ld + c, yv);
+  if (branches == 2) st_from_float(a_in + (m + (long long)B * rows) * ld + c, yv);
+}
+template <typename T>
+void cfg_euler(cudaStream_t st, float* y, const float* v, T* a_in, long long ld, int B, int branches, int rows,
+               int mel, float dt, float cfg, float* traj_slot) {
+  long long total = (long long)B * rows * mel;
+  cfg_euler_kernel<T><<<ceil_div_ll(total, 256), 256, 0, st>>>(y, v, a_in, ld, B, branches, rows, mel, dt, cfg,
+                                                               traj_slot, total);
+  F5B_POST_LAUNCH();
+}
+template void cfg_euler<float>(cudaStream_t, float*, const float*, float*, long long, int, int, int, int, float, float, float*);
+template void cfg_euler<bf16>(cudaStream_t, float*, const float*, bf16*, long long, int, int, int, int, float, float, float*);
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cast_mask_kernel(const float* __restrict__ x, T* __restrict__ out, int rows, int d4, const int* __restrict__ row_len,
+                 long long total4) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total4) return;
+  const long long m = i / d4;
+  float4 v = reinterpret_cast<const float4*>(x)[i];
+  if (row_len) {
+    const int b = (int)(m / rows), pos = (int)(m - (long long)b * rows);
+    if (pos >= row_len[b]) v = make_float4(0, 0, 0, 0);
+  }
+  store4<T>(out + i * 4, v.x, v.y, v.z, v.w);
+}
+template <typename T>
+void cast_mask(cudaStream_t st, const float* x, T* out, int batches, int rows, int d, const int* row_len) {
+  long long total4 = (long long)batches * rows * d / 4;
+  cast_mask_kernel<T><<<ceil_div_ll(total4, 256), 256, 0, st>>>(x, out, rows, d / 4, row_len, total4);
+  F5B_POST_LAUNCH();
+}
+template void cast_mask<float>(cudaStream_t, const float*, float*, int, int, int, const int*);
+template void cast_mask<bf16>(cudaStream_t, const float*, bf16*, int, int, int, const int*);
+
+__global__ void rope_table_kernel(float* __restrict__ cs, int rows, const float* __restrict__ inv_freq) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= rows * 32) return;
+  const int pos = i >> 5, j = i & 31;
+  const float ang = (float)pos * inv_freq[j];
+  cs[2 * i] = cosf(ang);
+  cs[2 * i + 1] = sinf(ang);
+}
+void rope_table(cudaStream_t st, float* cs, int rows, const float* inv_freq32) {
+  rope_table_kernel<<<(rows * 32 + 255) / 256, 256, 0, st>>>(cs, rows, inv_freq32);
+  F5B_POST_LAUNCH();
+}
+
+// SinusPositionEmbedding (modules.py:152-164): (1000 * t) * freq_j -> cat(sin, cos)
+__global__ void sinus_time_kernel(const float* __restrict__ t, int n, const float* __restrict__ freq,
+                                  float* __restrict__ out) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n * 128) return;
+  const int r = i >> 7, j = i & 127;
+  const float e = (1000.0f * t[r]) * freq[j];
+  out[r * 256 + j] = sinf(e);
+  out[r * 256 + 128 + j] = cosf(e);
+}
+void sinus_time(cudaStream_t st, const float* t, int n, const float* freq128, float* out) {
+  sinus_time_kernel<<<(n * 128 + 255) / 256, 256, 0, st>>>(t, n, freq128, out);
+  F5B_POST_LAUNCH();
+}
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, long long n) {
+  long long i = ((long long)blockIdx.x * 256 + threadIdx.x) * 4;
+  if (i + 4 <= n) {
+    float4 v = *reinterpret_cast<const float4*>(in + i);
+    store4<bf16>(out + i, v.x, v.y, v.z, v.w);
+  } else {
+    for (; i < n; ++i) out[i] = __float2bfloat16_rn(in[i]);
+  }
+}
+void f32_to_bf16(cudaStream_t st, const float* in, bf16* out, long long n) {
+  f32_to_bf16_kernel<<<ceil_div_ll((n + 3) / 4, 256), 256, 0, st>>>(in, out, n);
+  F5B_POST_LAUNCH();
+}
+void fill_zero(cudaStream_t st, void* p, size_t bytes) { F5B_CHECK_CUDA(cudaMemsetAsync(p, 0, bytes, st)); }
+
+// UNetT: x[b, 0, :] = t_emb[b % bmod], x[b, 1 + pos, :] = h[b, pos, :]
+__global__ void __launch_bounds__(256)
+unett_prepend_kernel(const float* __restrict__ temb, const float* __restrict__ h, float* __restrict__ x, int rows,
+                     int d4, int bmod, long long total4) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total4) return;
+  const long long m = i / d4;
+  const int c4 = (int)(i - m * d4);
+  const int b = (int)(m / (rows + 1)), pos = (int)(m - (long long)b * (rows + 1));
+  float4 v = pos == 0 ? reinterpret_cast<const float4*>(temb)[(long long)(b % bmod) * d4 + c4]
+                      : reinterpret_cast<const float4*>(h)[((long long)b * rows + pos - 1) * d4 + c4];
+  reinterpret_cast<float4*>(x)[i] = v;
+}
+void unett_prepend(cudaStream_t st, const float* temb, const float* h, float* x, int batches, int rows, int d,
+                   int temb_bmod) {
+  long long total4 = (long long)batches * (rows + 1) * d / 4;
+  unett_prepend_kernel<<<ceil_div_ll(total4, 256), 256, 0, st>>>(temb, h, x, rows, d / 4, temb_bmod, total4);
+  F5B_POST_LAUNCH();
+}
+template <typename T>
+__global__ void __launch_bounds__(256)
+concat2_kernel(const float* __restrict__ a, const float* __restrict__ b, T* __restrict__ out, int d4, long long total4) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total4) return;
+  const long long m = i / (2 * d4);
+  const int c4 = (int)(i - m * 2 * d4);
+  float4 v = c4 < d4 ? reinterpret_cast<const float4*>(a)[m * d4 + c4] : reinterpret_cast<const float4*>(b)[m * d4 + c4 - d4];
+  store4<T>(out + i * 4, v.x, v.y, v.z, v.w);
+}
+template <typename T>
+void concat2(cudaStream_t st, const float* a, const float* b, T* out, long long M, int d) {
+  long long total4 = M * 2 * d / 4;
+  concat2_kernel<T><<<ceil_div_ll(total4, 256), 256, 0, st>>>(a, b, out, d / 4, total4);
+  F5B_POST_LAUNCH();
+}
+template void concat2<float>(cudaStream_t, const float*, const float*, float*, long long, int);
+template void concat2<bf16>(cudaStream_t, const float*, const float*, bf16*, long long, int);
+
+}  // namespace f5b

@@ -1,0 +1,238 @@
+// Runtime plumbing: errors, arena, weight store, contraction dispatch, kernel-level C entry points.
+#include <atomic>
+#include <cstring>
+
+#include "plan.h"
+
+namespace f5b {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+const char* get_error() { return g_err.c_str(); }
+
+static std::atomic<long long> g_launches{0};
+void count_launch(long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
+static thread_local long long g_last_call = 0;
+void set_last_call(long long n) { g_last_call = n; }
+long long last_call() { return g_last_call; }
+
+void* Arena::alloc(size_t bytes) {
+  void* p = nullptr;
+  size_t b = (bytes + 255) & ~size_t(255);
+  if (b == 0) b = 256;
+  F5B_CHECK_CUDA(cudaMalloc(&p, b));
+  blocks_.push_back(p);
+  total_ += b;
+  return p;
+}
+void Arena::release() {
+  for (void* p : blocks_) cudaFree(p);
+  blocks_.clear();
+  total_ = 0;
+}
+
+WeightStore::WeightStore(Arena* arena, const f5b_tensor* w, int n, cudaStream_t st) {
+  for (int i = 0; i < n; ++i) {
+    F5B_REQUIRE(w[i].name != nullptr && w[i].data != nullptr && w[i].numel > 0, "bad weight entry");
+    float* d = arena->alloc_n<float>((size_t)w[i].numel);
+    F5B_CHECK_CUDA(cudaMemcpyAsync(d, w[i].data, (size_t)w[i].numel * 4,
+                                   w[i].on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    map_[w[i].name] = Entry{d, w[i].numel};
+  }
+  F5B_CHECK_CUDA(cudaStreamSynchronize(st));
+}
+const float* WeightStore::get(const std::string& name, long long numel) const {
+  auto it = map_.find(name);
+  if (it == map_.end()) {
+    set_error("missing weight '" + name + "'");
+    throw Err{F5B_ERR_MISSING};
+  }
+  if (numel >= 0 && it->second.numel != numel) {
+    set_error("weight '" + name + "' has " + std::to_string(it->second.numel) + " elements, expected " +
+              std::to_string(numel));
+    throw Err{F5B_ERR_INVALID};
+  }
+  return it->second.p;
+}
+
+__global__ void pad_convert_kernel(const float* __restrict__ in, bf16* __restrict__ out, int K, long long ld,
+                                   long long total) {
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  long long r = i / ld;
+  int c = (int)(i - r * ld);
+  out[i] = __float2bfloat16_rn(c < K ? in[r * K + c] : 0.0f);
+}
+
+__global__ void widen_kernel(const bf16* __restrict__ in, float* __restrict__ o, long long n) {
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i < n) o[i] = __bfloat162float(in[i]);
+}
+
+WMat make_wmat(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K) {
+  WMat m;
+  m.f32 = w32;
+  m.N = N;
+  m.K = K;
+  m.ld32 = K;
+  if (ctx.mode == F5B_MODE_BF16) {
+    long long ld = (K + 7) / 8 * 8;
+    bf16* p = arena->alloc_n<bf16>((size_t)N * ld);
+    long long total = (long long)N * ld;
+    pad_convert_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(w32, p, K, ld, total);
+    F5B_POST_LAUNCH();
+    m.b16 = p;
+    m.ld16 = ld;
+  }
+  return m;
+}
+
+float* concat_rows(Arena* arena, cudaStream_t st, const std::vector<std::pair<const float*, long long>>& parts) {
+  long long total = 0;
+  for (auto& p : parts) total += p.second;
+  float* out = arena->alloc_n<float>((size_t)total);
+  long long off = 0;
+  for (auto& p : parts) {
+    F5B_CHECK_CUDA(cudaMemcpyAsync(out + off, p.first, (size_t)p.second * 4, cudaMemcpyDeviceToDevice, st));
+    off += p.second;
+  }
+  return out;
+}
+
+void run_gemm(const DeviceCtx& ctx, cudaStream_t st, const void* A, long long lda, long long M, const WMat& w,
+              const EpiParams& ep, int force_bn) {
+  if (ctx.mode == F5B_MODE_BF16) {
+    F5B_REQUIRE(w.b16 != nullptr, "bf16 weight missing");
+    F5B_REQUIRE(M < (1LL << 31), "GEMM rows overflow");
+    tc_gemm(st, ctx.sm_count, reinterpret_cast<const bf16*>(A), lda, (int)M, 1, w.b16, w.ld16, w.N, w.K, ep, nullptr,
+            force_bn);
+  } else {
+    simt_gemm(st, reinterpret_cast<const float*>(A), lda, M, w.f32, w.ld32, w.N, w.K, ep);
+  }
+}
+
+void copy_in(void* dst, const void* src, size_t bytes, int mem, cudaStream_t st) {
+  F5B_CHECK_CUDA(cudaMemcpyAsync(dst, src, bytes, mem == F5B_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+}
+void copy_out(void* dst, const void* src, size_t bytes, int mem, cudaStream_t st) {
+  F5B_CHECK_CUDA(cudaMemcpyAsync(dst, src, bytes, mem == F5B_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+}
+
+static void device_check_throw(int device) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    set_error(std::string("no CUDA device: libf5b200 has no CPU fallback (") + cudaGetErrorString(e) + ")");
+    throw Err{F5B_ERR_NO_DEVICE};
+  }
+  if (device < 0 || device >= n) {
+    set_error("device index out of range");
+    throw Err{F5B_ERR_NO_DEVICE};
+  }
+  cudaDeviceProp p;
+  F5B_CHECK_CUDA(cudaGetDeviceProperties(&p, device));
+  if (p.major != 10) {
+    set_error(std::string("device '") + p.name + "' is sm_" + std::to_string(p.major) + std::to_string(p.minor) +
+              "; libf5b200 is built for sm_100a only");
+    throw Err{F5B_ERR_NO_DEVICE};
+  }
+  F5B_CHECK_CUDA(cudaSetDevice(device));
+}
+
+static bool g_kernels_ready = false;
+DeviceCtx open_device(int device, int mode) {
+  device_check_throw(device);
+  DeviceCtx c;
+  c.device = device;
+  c.mode = mode;
+  cudaDeviceProp p;
+  F5B_CHECK_CUDA(cudaGetDeviceProperties(&p, device));
+  c.sm_count = p.multiProcessorCount;
+  if (!g_kernels_ready) {
+    tc_init_kernels();
+    tc_gemm_init_kernels();
+    simt_init_kernels();
+    g_kernels_ready = true;
+  }
+  return c;
+}
+
+}  // namespace f5b
+
+using namespace f5b;
+namespace f5b { __global__ void widen_kernel(const bf16*, float*, long long); }
+
+#define F5B_API_BEGIN try {
+#define F5B_API_END                                  \
+  }                                                  \
+  catch (const f5b::Err& e) { return e.code; }       \
+  catch (const std::exception& e) {                  \
+    f5b::set_error(std::string("exception: ") + e.what()); \
+    return F5B_ERR_CUDA;                             \
+  }                                                  \
+  return F5B_OK;
+
+namespace f5b { DeviceCtx open_device(int device, int mode); }
+
+extern "C" {
+
+const char* f5b_last_error(void) { return get_error(); }
+int f5b_version(void) { return 100; }
+int64_t f5b_launch_count(void) { return launch_count(); }
+int64_t f5b_last_call_launches(void) { return last_call(); }
+
+int f5b_device_check(int device) {
+  F5B_API_BEGIN
+  open_device(device, F5B_MODE_FP32);
+  F5B_API_END
+}
+
+int f5b_op_gemm(int32_t mode, const float* A, const float* W, const float* bias, int32_t M, int32_t N, int32_t K,
+                int32_t act, float* out, int32_t force_bn, int32_t device, void* stream) {
+  F5B_API_BEGIN
+  DeviceCtx ctx = open_device(device, mode);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  Arena arena;
+  WMat w = make_wmat(ctx, &arena, st, W, N, K);
+  EpiParams ep;
+  ep.act = act;
+  ep.bias = bias;
+  ep.out = out;
+  ep.ldo = N;
+  ep.n_valid = N;
+  if (mode == F5B_MODE_BF16) {
+    WMat tmp = make_wmat(ctx, &arena, st, A, M, K);  // pad K to a multiple of 8 and convert, like a weight
+    run_gemm(ctx, st, tmp.b16, tmp.ld16, M, w, ep, force_bn);
+  } else {
+    run_gemm(ctx, st, A, K, M, w, ep, 0);
+  }
+  F5B_CHECK_CUDA(cudaStreamSynchronize(st));
+  F5B_API_END
+}
+
+int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int32_t batches, int32_t rows,
+                     int32_t heads, float* out, int32_t device, void* stream) {
+  F5B_API_BEGIN
+  DeviceCtx ctx = open_device(device, mode);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const long long M = (long long)batches * rows;
+  const int inner = heads * 64;
+  if (mode == F5B_MODE_BF16) {
+    Arena arena;
+    bf16* q16 = arena.alloc_n<bf16>((size_t)M * 3 * inner);
+    bf16* o16 = arena.alloc_n<bf16>((size_t)M * inner);
+    f32_to_bf16(st, qkv, q16, M * 3 * inner);
+    tc_attention(st, q16, o16, batches, rows, heads, kv_len, 0.125f);
+    widen_kernel<<<(unsigned)((M * inner + 255) / 256), 256, 0, st>>>(o16, out, M * inner);
+    F5B_POST_LAUNCH();
+    F5B_CHECK_CUDA(cudaStreamSynchronize(st));
+  } else {
+    simt_attention(st, qkv, out, batches, rows, heads, kv_len, 0.125f);
+    F5B_CHECK_CUDA(cudaStreamSynchronize(st));
+  }
+  F5B_API_END
+}
+
+}  // extern "C"

@@ -1,0 +1,57 @@
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include "common.cuh"
+
+namespace f5b {
+
+struct TcGemmShape {
+  int rows_per_batch;
+  int batches;
+  int tiles_m_per_batch;
+  int tiles_n;
+  int N;
+  int num_kb;
+  int conv;
+  int conv_kb_per_tap;
+  int conv_pad;
+  int conv_cg;
+};
+
+// Grouped 1-D convolution expressed as a GEMM: K index = tap * cg + ci, A column = group * cg + ci,
+// A row = output row + tap - pad (zero outside [0, rows_per_batch)).
+struct TcConv {
+  int taps;      // kernel size (31)
+  int pad;       // 15
+  int cg;        // channels per group
+  int channels;  // total input channels (width of A)
+};
+
+void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                    const uint32_t* box);
+
+// bf16 tensor-core GEMM: out = epilogue(A[rows, K] * W[N, K]^T).  A rows are [batches][rows_per_batch] with a
+// common leading dimension lda (elements).
+void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int rows_per_batch, int batches,
+             const bf16* W, long long ldw, int N, int K, const EpiParams& ep, const TcConv* conv, int force_bn);
+
+// fp32 CUDA-core GEMM with the same epilogue (the correctness mode; also used for the tiny per-sample tables).
+void simt_gemm(cudaStream_t st, const float* A, long long lda, long long M, const float* W, long long ldw, int N,
+               int K, const EpiParams& ep);
+
+// fp32 grouped conv (k taps, groups) + epilogue; x [batches, rows, channels], w rearranged [groups][taps][cg_in][cg_out].
+void simt_group_conv(cudaStream_t st, const float* x, int batches, int rows, int channels, const float* w_r, int taps,
+                     int pad, int groups, const EpiParams& ep);
+
+// bf16 tensor-core attention (tcgen05) and fp32 CUDA-core attention.  qkv [batches*rows, 3*heads*64]; out
+// [batches*rows, heads*64].  kv_len[b] (or rows when null) keys take part.
+void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int rows, int heads, const int* kv_len,
+                  float scale);
+void simt_attention(cudaStream_t st, const float* qkv, float* out, int batches, int rows, int heads, const int* kv_len,
+                    float scale);
+
+void tc_init_kernels();       // attention
+void tc_gemm_init_kernels();  // GEMM
+void simt_init_kernels();
+
+}  // namespace f5b

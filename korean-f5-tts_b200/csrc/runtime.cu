@@ -235,4 +235,58 @@ int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int3
   F5B_API_END
 }
 
+
+int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, float* ms, int32_t device, void* stream) {
+  F5B_API_BEGIN
+  F5B_REQUIRE(ms != nullptr && iters > 0, "bad argument");
+  DeviceCtx ctx = open_device(device, F5B_MODE_BF16);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  Arena arena;
+  cudaEvent_t e0, e1;
+  F5B_CHECK_CUDA(cudaEventCreate(&e0));
+  F5B_CHECK_CUDA(cudaEventCreate(&e1));
+  auto timed = [&](auto&& fn) {
+    for (int i = 0; i < 3; ++i) fn();
+    F5B_CHECK_CUDA(cudaEventRecord(e0, st));
+    for (int i = 0; i < iters; ++i) fn();
+    F5B_CHECK_CUDA(cudaEventRecord(e1, st));
+    F5B_CHECK_CUDA(cudaEventSynchronize(e1));
+    float t = 0;
+    F5B_CHECK_CUDA(cudaEventElapsedTime(&t, e0, e1));
+    *ms = t / iters;
+  };
+  if (which == 0) {
+    long long ld = (K + 7) / 8 * 8;
+    bf16* A = arena.alloc_n<bf16>((size_t)M * ld);
+    bf16* W = arena.alloc_n<bf16>((size_t)N * ld);
+    bf16* O = arena.alloc_n<bf16>((size_t)M * N);
+    F5B_CHECK_CUDA(cudaMemsetAsync(A, 0x3c, (size_t)M * ld * 2, st));
+    F5B_CHECK_CUDA(cudaMemsetAsync(W, 0x3c, (size_t)N * ld * 2, st));
+    EpiParams ep;
+    ep.out = O;
+    ep.out_bf16 = 1;
+    ep.ldo = N;
+    ep.n_valid = N;
+    timed([&] { tc_gemm(st, ctx.sm_count, A, ld, M, 1, W, ld, N, K, ep, nullptr, 0); });
+  } else if (which == 1) {
+    const int rows = M, heads = N, batches = K, inner = heads * 64;
+    bf16* Q = arena.alloc_n<bf16>((size_t)batches * rows * 3 * inner);
+    bf16* O = arena.alloc_n<bf16>((size_t)batches * rows * inner);
+    F5B_CHECK_CUDA(cudaMemsetAsync(Q, 0x3c, (size_t)batches * rows * 3 * inner * 2, st));
+    timed([&] { tc_attention(st, Q, O, batches, rows, heads, nullptr, 0.125f); });
+  } else if (which == 2) {
+    float* X = arena.alloc_n<float>((size_t)M * N);
+    bf16* O = arena.alloc_n<bf16>((size_t)M * N);
+    float* V = arena.alloc_n<float>((size_t)2 * N);
+    F5B_CHECK_CUDA(cudaMemsetAsync(X, 0x3c, (size_t)M * N * 4, st));
+    F5B_CHECK_CUDA(cudaMemsetAsync(V, 0, (size_t)2 * N * 4, st));
+    timed([&] { ln_mod<bf16>(st, X, O, M, N, V, V + N, 1.0f, 0, 1 << 30, 1, 1e-6f); });
+  } else {
+    F5B_REQUIRE(false, "unknown kernel selector");
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  F5B_API_END
+}
+
 }  // extern "C"

@@ -1,0 +1,44 @@
+"""Request sharding for multi-GPU inference: utterances are independent, so each GPU takes a disjoint shard and no
+collective runs on the data path (the reference shards the same way with `accelerator.split_between_processes`,
+src/f5_tts/eval/eval_infer_batch.py:181, and `DistributedSampler`, runtime/triton_trtllm/benchmark.py:340-341).
+
+Unlike the reference's contiguous split, shards are balanced by an attention-aware cost and each shard is cut into
+length-sorted micro-batches so padding waste inside a batch stays small."""
+from __future__ import annotations
+
+from typing import List, Sequence
+
+
+def request_cost(n_frames: int, dim: int = 1024, depth: int = 22, ff_mult: int = 2) -> float:
+    """Algorithmic flops of one CFG-doubled backbone evaluation over n_frames: per token per layer
+    (8 + 4 ff_mult) d^2 for the projections and 4 n d for attention; times two branches."""
+    per_token = depth * ((8 + 4 * ff_mult) * dim * dim + 4 * n_frames * dim)
+    return 2.0 * n_frames * per_token
+
+
+def shard_requests(lengths: Sequence[int], world_size: int, **cost_kw) -> List[List[int]]:
+    """Longest-processing-time-first assignment.  Deterministic; every index appears in exactly one shard."""
+    order = sorted(range(len(lengths)), key=lambda i: (-lengths[i], i))
+    loads = [0.0] * world_size
+    shards: List[List[int]] = [[] for _ in range(world_size)]
+    for i in order:
+        r = min(range(world_size), key=lambda k: (loads[k], k))
+        shards[r].append(i)
+        loads[r] += request_cost(lengths[i], **cost_kw)
+    return shards
+
+
+def micro_batches(indices: Sequence[int], lengths: Sequence[int], max_rows: int, max_batch: int = 64) -> List[List[int]]:
+    """Cut a shard into batches of similar length: sorted by length, a batch closes when batch_size * longest would
+    exceed max_rows (padded rows) or max_batch utterances."""
+    out: List[List[int]] = []
+    cur: List[int] = []
+    for i in sorted(indices, key=lambda j: (-lengths[j], j)):
+        longest = lengths[cur[0]] if cur else lengths[i]
+        if cur and ((len(cur) + 1) * longest > max_rows or len(cur) >= max_batch):
+            out.append(cur)
+            cur = []
+        cur.append(i)
+    if cur:
+        out.append(cur)
+    return out

@@ -1,0 +1,112 @@
+"""Kernel-level parity through the C ABI (f5b_op_*): every contraction kernel against a plain PyTorch fp32 reference
+of the same op (computed on the host).  Tolerances: fp32 kernels 1e-4 relative to the output scale; bf16 tensor-core
+kernels 2e-2 relative (bf16 operand rounding, fp32 accumulation)."""
+import ctypes as C
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _lib():
+    from f5b200 import _lib as L
+
+    return L
+
+
+def _gemm(mode, a, w, bias, act="none", force_bn=0):
+    L = _lib()
+    dev = torch.device("cuda", 0)
+    a_d, w_d = a.to(dev).contiguous(), w.to(dev).contiguous()
+    b_d = bias.to(dev).contiguous() if bias is not None else None
+    out = torch.empty((a.shape[0], w.shape[0]), device=dev)
+    L.check(L.lib().f5b_op_gemm(mode, a_d.data_ptr(), w_d.data_ptr(), L.ptr(b_d), a.shape[0], w.shape[0], a.shape[1],
+                                L.ACT[act], out.data_ptr(), force_bn, 0, 0))
+    return out.cpu()
+
+
+def _ref_act(x, act):
+    import torch.nn.functional as F
+
+    return {"none": lambda t: t, "gelu_tanh": lambda t: F.gelu(t, approximate="tanh"), "gelu": F.gelu, "mish": F.mish,
+            "silu": F.silu}[act](x)
+
+
+@pytest.mark.parametrize("M,N,K,act", [(300, 256, 128, "none"), (1880, 1024, 712, "gelu_tanh"), (16, 4100, 1024, "silu"),
+                                       (33, 100, 300, "mish"), (129, 132, 64, "gelu")])
+def test_gemm_fp32(M, N, K, act):
+    g = torch.Generator().manual_seed(M + N)
+    a = torch.randn(M, K, generator=g)
+    w = torch.randn(N, K, generator=g) * K ** -0.5
+    b = torch.randn(N, generator=g) * 0.1
+    out = _gemm(0, a, w, b, act)
+    ref = _ref_act(a.double() @ w.double().T + b.double(), act).float()
+    assert (out - ref).abs().max() <= 1e-4 * max(1.0, float(ref.abs().max()))
+
+
+@pytest.mark.parametrize("M,N,K,act,bn", [(128, 128, 64, "none", 128), (256, 256, 256, "none", 64),
+                                          (1880, 3072, 1024, "none", 0), (1880, 1024, 2048, "gelu_tanh", 256),
+                                          (1880, 100, 1024, "none", 64), (940, 1024, 712, "none", 128),
+                                          (77, 520, 1000, "gelu", 0)])
+def test_gemm_bf16_tcgen05(M, N, K, act, bn):
+    g = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn(M, K, generator=g)
+    w = torch.randn(N, K, generator=g) * K ** -0.5
+    b = torch.randn(N, generator=g) * 0.1
+    out = _gemm(1, a, w, b, act, bn)
+    ar, wr = a.bfloat16().double(), w.bfloat16().double()  # the kernel rounds operands to bf16, accumulates in fp32
+    ref = _ref_act(ar @ wr.T + b.double(), act).float()
+    err = (out - ref).abs().max()
+    assert err <= 2e-3 * max(1.0, float(ref.abs().max())), f"max err {err}"
+
+
+def _attention(mode, qkv, kv_len, batches, rows, heads):
+    L = _lib()
+    dev = torch.device("cuda", 0)
+    q_d = qkv.to(dev).contiguous()
+    l_d = kv_len.to(dev, torch.int32).contiguous() if kv_len is not None else None
+    out = torch.empty((batches * rows, heads * 64), device=dev)
+    L.check(L.lib().f5b_op_attention(mode, q_d.data_ptr(), L.ptr(l_d), batches, rows, heads, out.data_ptr(), 0, 0))
+    return out.cpu()
+
+
+def _attention_ref(qkv, kv_len, batches, rows, heads):
+    inner = heads * 64
+    x = qkv.double().view(batches, rows, 3, heads, 64)
+    q, k, v = (x[:, :, i].transpose(1, 2) for i in range(3))
+    s = q @ k.transpose(-1, -2) * 0.125
+    if kv_len is not None:
+        keep = torch.arange(rows)[None, :] < kv_len[:, None]
+        s = s.masked_fill(~keep[:, None, None, :], float("-inf"))
+    o = torch.softmax(s, -1) @ v
+    return o.transpose(1, 2).reshape(batches * rows, inner).float()
+
+
+@pytest.mark.parametrize("batches,rows,heads,lens", [(1, 100, 2, None), (2, 333, 3, [333, 201]), (2, 940, 16, None)])
+def test_attention_fp32(batches, rows, heads, lens):
+    g = torch.Generator().manual_seed(rows)
+    qkv = torch.randn(batches * rows, 3 * heads * 64, generator=g)
+    kv = torch.tensor(lens) if lens else None
+    out = _attention(0, qkv, kv, batches, rows, heads)
+    ref = _attention_ref(qkv, kv, batches, rows, heads)
+    assert (out - ref).abs().max() <= 1e-4
+
+
+@pytest.mark.parametrize("batches,rows,heads,lens", [(1, 128, 1, None), (1, 100, 2, None), (2, 333, 3, [333, 201]),
+                                                     (2, 940, 16, None), (1, 2801, 4, None)])
+def test_attention_bf16_tcgen05(batches, rows, heads, lens):
+    g = torch.Generator().manual_seed(rows + 1)
+    qkv = torch.randn(batches * rows, 3 * heads * 64, generator=g)
+    kv = torch.tensor(lens) if lens else None
+    out = _attention(1, qkv, kv, batches, rows, heads)
+    ref = _attention_ref(qkv.bfloat16().float(), kv, batches, rows, heads)
+    err = (out - ref).abs().max()
+    assert err <= 2e-2, f"max err {err}"  # P and the output are rounded to bf16
+
+
+def test_op_time_runs():
+    L = _lib()
+    ms = C.c_float()
+    L.check(L.lib().f5b_op_time(0, 512, 512, 512, 3, C.byref(ms), 0, 0))
+    assert ms.value > 0

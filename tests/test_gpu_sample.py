@@ -1,0 +1,136 @@
+"""End-to-end parity of the CUDA path (through f5b200.CFM.sample -> C ABI f5b_sample) against
+  (a) the committed golden vectors produced by the UNMODIFIED reference modules (tests/golden/, oracle/make_golden.py),
+  (b) the CPU oracle run on the same seeded inputs, weights and initial noise.
+Tolerances are the north star's: fp32 mode max-abs 1e-3 on the final mel; bf16 mode max-abs 2e-2 versus the fp32 oracle.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import O, build_backbone, build_cfm, max_abs
+
+pytestmark = pytest.mark.gpu
+
+from oracle.make_golden import CASES, case_inputs  # noqa: E402  (checker only; does not touch /root/reference)
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_golden_fp32(name, golden_dir):
+    cfg, cond, text, lens, durs, steps, cfgs, sway = case_inputs(name)
+    sd = O.synth_backbone_weights(cfg, seed=11)
+    gold = np.load(os.path.join(golden_dir, name + ".npz"))
+    assert abs(float(sum(v.double().abs().sum() for v in sd.values())) - float(gold["weight_abs_sum"])) < 1e-3
+    ref = O.cfm_sample(sd, cfg, cond, text, durs, lens=lens, steps=steps, cfg_strength=cfgs, sway_sampling_coef=sway,
+                       seed=5)  # supplies the seeded CPU noise the reference used
+    cfm = build_cfm(cfg, sd, "fp32")
+    out, traj = cfm.sample(cond=cond.cuda(), text=text.cuda(), duration=durs.cuda(), lens=lens.cuda(), steps=steps,
+                           cfg_strength=cfgs, sway_sampling_coef=sway, y0=ref.y0)
+    assert tuple(out.shape) == gold["out"].shape and traj.shape[0] == steps + 1
+    assert max_abs(traj[1], gold["traj_first"]) <= 1e-3
+    assert max_abs(traj[steps // 2], gold["traj_mid"]) <= 1e-3
+    assert max_abs(out, gold["out"]) <= 1e-3  # fp32 mode: final mel max-abs 1e-3
+
+
+def test_forward_api_fp32():
+    cfg = O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2, attn_mask_enabled=True)
+    sd = O.synth_backbone_weights(cfg, seed=3)
+    cond, text = O.synth_inputs(50, 50, 9, batch=2, seed=4)
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(2, 50, 100, generator=g)
+    time = torch.tensor([0.3, 0.7])
+    mask = O.lens_to_mask(torch.tensor([50, 37]))
+    m = build_backbone(cfg, sd, "fp32")
+    for kw in (dict(cfg_infer=True), dict(drop_audio_cond=True, drop_text=True), dict()):
+        ref = O.dit_forward(sd, cfg, x, cond, text, time, mask, kw.get("drop_audio_cond", False),
+                            kw.get("drop_text", False), kw.get("cfg_infer", False))
+        out = m(x.cuda(), cond.cuda(), text.cuda(), time, mask=mask.cuda(), **kw)
+        keep = torch.cat([mask, mask]) if kw.get("cfg_infer") else mask
+        assert max_abs(out.cpu() * keep[..., None], ref * keep[..., None]) <= 1e-3
+
+
+@pytest.mark.parametrize("backbone,N,B", [("DiT", 300, 1), ("DiT", 200, 2), ("UNetT", 260, 1)])
+def test_bf16_vs_fp32_oracle(backbone, N, B):
+    """bf16 tensor-core mode on a full-width (dim 1024) model, reduced depth so the CPU oracle takes seconds."""
+    if backbone == "DiT":
+        cfg = O.ArchCfg.named("F5TTS_v1_Base", depth=3, attn_mask_enabled=(B > 1))
+    else:
+        cfg = O.ArchCfg.named("E2TTS_Base", depth=4)
+    sd = O.synth_backbone_weights(cfg, seed=21)
+    nref = N // 3
+    cond, text = O.synth_inputs(N, nref, 40, batch=B, seed=8)
+    lens = torch.tensor([nref, nref - 20][:B])
+    durs = torch.tensor([N, N - 40][:B])
+    steps = 6
+    ref = O.cfm_sample(sd, cfg, cond, text, durs, lens=lens, steps=steps, cfg_strength=2.0, sway_sampling_coef=-1.0, seed=1)
+    cfm = build_cfm(cfg, sd, "bf16")
+    out, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), duration=durs.cuda(), lens=lens.cuda(), steps=steps,
+                        cfg_strength=2.0, sway_sampling_coef=-1.0, y0=ref.y0)
+    keep = O.lens_to_mask(durs)[..., None] if B > 1 else torch.ones(1, N, 1, dtype=torch.bool)
+    err = max_abs(out.cpu() * keep, ref.out * keep)
+    print(f"bf16 {backbone} N={N} B={B}: max-abs {err:.4e}")
+    assert err <= 2e-2
+    # the same model in fp32 mode must hit the tight tolerance
+    cfm32 = build_cfm(cfg, sd, "fp32")
+    out32, _ = cfm32.sample(cond=cond.cuda(), text=text.cuda(), duration=durs.cuda(), lens=lens.cuda(), steps=steps,
+                            cfg_strength=2.0, sway_sampling_coef=-1.0, y0=ref.y0)
+    assert max_abs(out32.cpu() * keep, ref.out * keep) <= 1e-3
+
+
+def test_host_buffers_and_graph_replay():
+    """mem=HOST path (the e2e leg of bench.py) and CUDA-graph replay give the same bits as the device-pointer path."""
+    cfg = O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2)
+    sd = O.synth_backbone_weights(cfg, seed=2)
+    cond, text = O.synth_inputs(60, 20, 7, seed=1)
+    g = torch.Generator().manual_seed(3)
+    y0 = torch.randn(1, 60, 100, generator=g)
+    cfm = build_cfm(cfg, sd, "fp32")
+    kw = dict(duration=60, steps=4, cfg_strength=2.0, sway_sampling_coef=-1.0)
+    a, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)
+    b, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)  # graph replay
+    c, _ = cfm.sample(cond=cond, text=text, y0=y0, **kw)  # host pointers
+    assert torch.equal(a, b) and torch.equal(a.cpu(), c.cpu())
+
+
+def test_mel_frontend_golden(golden_dir):
+    import f5b200
+
+    g = torch.Generator().manual_seed(3)
+    wav = torch.randn(2, 24000, generator=g) * 0.1
+    gold = np.load(os.path.join(golden_dir, "mel_frontend.npz"))["mel"]
+    mel = f5b200.MelSpec()(wav.cuda())
+    assert tuple(mel.shape) == gold.shape
+    assert max_abs(mel, gold) <= 1e-3
+    assert max_abs(f5b200.MelSpec()(wav), gold) <= 1e-3  # host-memory path
+
+
+@pytest.mark.parametrize("T,B", [(50, 1), (333, 2)])
+def test_vocos_decode(T, B):
+    import f5b200
+    from helpers import snr_db
+
+    sd = O.synth_vocos_weights(0)
+    g = torch.Generator().manual_seed(T)
+    mel = (torch.randn(B, 100, T, generator=g) * 2.0 - 3.0).clamp(min=-11.5)
+    ref = O.vocos_decode(sd, mel)
+    voc = f5b200.Vocos(precision="fp32")
+    voc.load_state_dict(sd)
+    wav = voc.cuda().decode(mel.cuda())
+    assert tuple(wav.shape) == (B, (T - 1) * 256)
+    scale = float(ref.abs().max())
+    assert max_abs(wav, ref) <= 1e-3 * max(1.0, scale)  # fp32 mode: waveform 1e-3
+    voc16 = f5b200.Vocos(precision="bf16")
+    voc16.load_state_dict(sd)
+    wav16 = voc16.cuda().decode(mel.cuda())
+    s = snr_db(ref, wav16)
+    print(f"vocos bf16 SNR {s:.1f} dB (T={T})")
+    assert s >= 40.0  # bf16 mode: waveform SNR >= 40 dB versus the fp32 reference
+
+
+def test_missing_weight_is_loud():
+    import f5b200
+
+    m = f5b200.DiT(dim=128, depth=1, heads=2, ff_mult=2, text_dim=64, conv_layers=1, text_num_embeds=10, precision="fp32")
+    with pytest.raises(f5b200.F5BError):
+        m(torch.zeros(1, 8, 100), torch.zeros(1, 8, 100), torch.zeros(1, 3, dtype=torch.long), torch.tensor(0.5))

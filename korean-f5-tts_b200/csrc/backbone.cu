@@ -115,6 +115,7 @@ struct f5b_plan {
   long long gnodes = 0;
   long long last_call_launches = 0;
   bool use_graph = true;
+  cudaStream_t own_stream = nullptr;  // used when the caller passes the (uncapturable) legacy default stream
 
   f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, int device);
   ~f5b_plan();
@@ -134,7 +135,10 @@ struct f5b_plan {
   }
 };
 
-f5b_plan::~f5b_plan() { drop_graph(); }
+f5b_plan::~f5b_plan() {
+  drop_graph();
+  if (own_stream) cudaStreamDestroy(own_stream);
+}
 
 f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, int device) : a(arch) {
   F5B_REQUIRE(mode == F5B_MODE_FP32 || mode == F5B_MODE_BF16, "unknown precision mode");
@@ -143,6 +147,7 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
   F5B_REQUIRE(a.dim % 16 == 0 && a.mel_dim % 4 == 0 && a.text_dim % 4 == 0, "unsupported widths");
   ctx = open_device(device, mode);
   use_graph = std::getenv("F5B_NO_GRAPH") == nullptr;
+  F5B_CHECK_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
   is_dit = a.backbone == F5B_BACKBONE_DIT;
   inner = a.heads * 64;
   R_extra = is_dit ? 0 : 1;

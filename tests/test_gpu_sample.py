@@ -79,7 +79,8 @@ def test_bf16_vs_fp32_oracle(backbone, N, B):
 
 
 def test_host_buffers_and_graph_replay():
-    """mem=HOST path (the e2e leg of bench.py) and CUDA-graph replay give the same bits as the device-pointer path."""
+    """CUDA-graph replay gives the same bits; the mem=HOST path (the e2e leg of bench.py) agrees to rounding (its time
+    grid is evaluated by the host's cos() instead of the device's, as in the reference when the model sits on CPU)."""
     cfg = O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2)
     sd = O.synth_backbone_weights(cfg, seed=2)
     cond, text = O.synth_inputs(60, 20, 7, seed=1)
@@ -90,7 +91,8 @@ def test_host_buffers_and_graph_replay():
     a, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)
     b, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)  # graph replay
     c, _ = cfm.sample(cond=cond, text=text, y0=y0, **kw)  # host pointers
-    assert torch.equal(a, b) and torch.equal(a.cpu(), c.cpu())
+    assert torch.equal(a, b)
+    assert max_abs(a, c) <= 1e-4
 
 
 def test_mel_frontend_golden(golden_dir):

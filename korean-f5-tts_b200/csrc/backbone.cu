@@ -29,7 +29,7 @@ __global__ void conv_w_rearrange_f32(const float* __restrict__ w, float* __restr
   int co = g * cg + co_l;
   out[i] = w[((long long)co * cg + ci) * taps + tap];
 }
-__global__ void conv_w_rearrange_bf16(const float* __restrict__ w, bf16* __restrict__ out, int d, int cg, int taps) {
+__global__ void conv_w_rearrange_f16(const float* __restrict__ w, __half* __restrict__ out, int d, int cg, int taps) {
   // w [d, cg, taps] -> out [co][tap*cg + ci]
   long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   long long total = (long long)d * cg * taps;
@@ -38,7 +38,7 @@ __global__ void conv_w_rearrange_bf16(const float* __restrict__ w, bf16* __restr
   long long r = i / cg;
   int tap = (int)(r % taps);
   int co = (int)(r / taps);
-  out[i] = __float2bfloat16_rn(w[((long long)co * cg + ci) * taps + tap]);
+  out[i] = __float2half_rn(w[((long long)co * cg + ci) * taps + tap]);
 }
 __global__ void dw_transpose(const float* __restrict__ w, float* __restrict__ out, int d) {
   int i = blockIdx.x * 256 + threadIdx.x;
@@ -64,12 +64,12 @@ struct Layer {
 struct Bufs {
   long long cap_rows = 0;  // batches * R
   int capB = 0, cap_nt = 0, cap_steps = 0, capN = 0;
-  float *y, *cond, *v_out, *x, *hproj, *te, *sin_emb, *h1, *st_emb, *ada, *rope_cs, *t_dev, *grn_scratch, *traj;
+  float *y, *cond, *v_out, *x, *hproj, *hconst, *a_in, *te, *sin_emb, *h1, *st_emb, *ada, *rope_cs, *t_dev, *grn_scratch, *traj;
   long long traj_cap = 0;
   long long* text;
   int *lens_in, *lens2, *lens2p1;
   unsigned char* keep;
-  void *a_in, *c_in, *c_mid, *norm, *qkv, *attn_o, *ffh, *tnorm, *th, *cat;
+  void *c_in, *c_mid, *norm, *norm3, *qkv, *attn_o, *ffh, *tnorm, *th, *cat;
   std::vector<float*> skips;
 };
 
@@ -102,7 +102,7 @@ struct f5b_plan {
   const float *b_in, *b_out, *tm0_w, *tm0_b, *tm2_w, *tm2_b, *emb_table, *norm_out_g = nullptr;
   const float* conv_b[2];
   const float* conv_w_r[2] = {nullptr, nullptr};
-  const bf16* conv_w16[2] = {nullptr, nullptr};
+  const __half* conv_w16[2] = {nullptr, nullptr};  // fp16: see input_embed
   float *ada_w = nullptr, *ada_b = nullptr;
   int ada_W = 0;
   float *inv_freq_text, *inv_freq_rope, *time_freq;
@@ -122,6 +122,7 @@ struct f5b_plan {
   void ensure_ws(int B, int N, int nt, int steps, bool want_traj);
   template <typename T> void text_embed(cudaStream_t st, int B, int N, int nt, int batches, int text_uncond_from,
                                         int cond_uncond_from, const int* lens_text);
+  void const_inputs(cudaStream_t st, int B, int batches, int N, int cond_uncond_from);
   template <typename T> void tables(cudaStream_t st, int n_t);
   template <typename T> void input_embed(cudaStream_t st, int batches, int N, const int* lens2);
   template <typename T> void eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int tbl_bmod,
@@ -185,7 +186,10 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
     tb.b2 = W(p + ".pwconv2.bias", td);
     tblocks.push_back(tb);
   }
-  in_proj = make_wmat(ctx, &warena, st, W("input_embed.proj.weight", (long long)d * kin), d, kin);
+  in_proj.f32 = W("input_embed.proj.weight", (long long)d * kin);  // contracted in fp32 in both modes (const_inputs)
+  in_proj.N = d;
+  in_proj.K = kin;
+  in_proj.ld32 = kin;
   b_in = W("input_embed.proj.bias", d);
   const int cg = d / 16;
   for (int c = 0; c < 2; ++c) {
@@ -194,8 +198,8 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
     conv_b[c] = W(p + ".bias", d);
     long long total = (long long)d * cg * 31;
     if (mode == F5B_MODE_BF16) {
-      bf16* o = warena.alloc_n<bf16>((size_t)total);
-      conv_w_rearrange_bf16<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(cw, o, d, cg, 31);
+      __half* o = warena.alloc_n<__half>((size_t)total);
+      conv_w_rearrange_f16<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(cw, o, d, cg, 31);
       conv_w16[c] = o;
     } else {
       float* o = warena.alloc_n<float>((size_t)total);
@@ -248,7 +252,8 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
   } else {
     norm_out_g = W("norm_out.g", d);
   }
-  proj_out = make_wmat(ctx, &warena, st, W("proj_out.weight", (long long)a.mel_dim * d), a.mel_dim, d);
+  // the velocity goes straight into the ODE state: proj_out is contracted with ~16-bit operands in bf16 mode
+  proj_out = make_wmat_split3(ctx, &warena, st, W("proj_out.weight", (long long)a.mel_dim * d), a.mel_dim, d);
   b_out = W("proj_out.bias", a.mel_dim);
 
   // frequency tables, computed the way the reference does (fp32 pow / exp of fp32 arguments)
@@ -304,11 +309,13 @@ void f5b_plan::ensure_ws(int B, int N, int nt, int steps, bool want_traj) {
   bf.lens2 = A.alloc_n<int>((size_t)2 * B);
   bf.lens2p1 = A.alloc_n<int>((size_t)2 * B);
   bf.keep = A.alloc_n<unsigned char>((size_t)2 * B * N);
-  bf.a_in = A.alloc((size_t)2 * B * N * kin_ld * es);
-  F5B_CHECK_CUDA(cudaMemset(bf.a_in, 0, (size_t)2 * B * N * kin_ld * es));
+  bf.hconst = A.alloc_n<float>((size_t)2 * B * N * d);
+  bf.a_in = A.alloc_n<float>((size_t)2 * B * N * kin_ld);
+  F5B_CHECK_CUDA(cudaMemset(bf.a_in, 0, (size_t)2 * B * N * kin_ld * 4));
   bf.c_in = A.alloc((size_t)rows * d * es);
   bf.c_mid = A.alloc((size_t)rows * d * es);
   bf.norm = A.alloc((size_t)rows * d * es);
+  bf.norm3 = ctx.mode == F5B_MODE_BF16 ? A.alloc((size_t)rows * 3 * d * 2) : nullptr;
   bf.qkv = A.alloc((size_t)rows * 3 * inner * es);
   bf.attn_o = A.alloc((size_t)rows * inner * es);
   bf.ffh = A.alloc((size_t)rows * ffd * es);
@@ -340,7 +347,7 @@ void f5b_plan::text_embed(cudaStream_t st, int B, int N, int nt, int batches, in
     e1.act = ACT_GELU_ERF;
     e1.bias = tb.b1;
     e1.out = bf.th;
-    e1.out_bf16 = sizeof(T) == 2;
+    e1.out_type = sizeof(T) == 2;
     e1.ldo = 2 * td;
     e1.n_valid = 2 * td;
     run_gemm(ctx, st, bf.tnorm, td, M, tb.pw1, e1);
@@ -354,7 +361,21 @@ void f5b_plan::text_embed(cudaStream_t st, int B, int N, int nt, int batches, in
     run_gemm(ctx, st, bf.th, 2 * td, M, tb.pw2, e2);
     if (need_mask) mask_rows(st, bf.te, M, td, bf.keep);
   }
-  build_a_in<T>(st, (T*)bf.a_in, kin_ld, B, batches, N, a.mel_dim, td, bf.cond, bf.te, cond_uncond_from);
+  const_inputs(st, B, batches, N, cond_uncond_from);
+}
+
+// The input projection (dit.py:124,138 / unett.py:92,99) is linear in cat(x, cond, text): the cond / text columns do
+// not change during the ODE, so their contribution (+ bias) is contracted once per call, in fp32, into bf.hconst;
+// every evaluation only adds the K = mel_dim x-columns (fp32 as well: the ODE state never passes through bf16).
+void f5b_plan::const_inputs(cudaStream_t st, int B, int batches, int N, int cond_uncond_from) {
+  const int mel = a.mel_dim, d = a.dim;
+  build_a_in(st, bf.a_in, kin_ld, B, batches, N, mel, td, bf.cond, bf.te, cond_uncond_from);
+  EpiParams e;
+  e.bias = b_in;
+  e.out = bf.hconst;
+  e.ldo = d;
+  e.n_valid = d;
+  simt_gemm(st, bf.a_in + mel, kin_ld, (long long)batches * N, in_proj.f32 + mel, kin, d, kin - mel, e);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -397,12 +418,16 @@ void f5b_plan::input_embed(cudaStream_t st, int batches, int N, const int* lens_
   const long long M = (long long)batches * N;
   const bool is16 = sizeof(T) == 2;
   EpiParams e;
-  e.bias = b_in;
   e.out = bf.hproj;
   e.ldo = d;
   e.n_valid = d;
-  run_gemm(ctx, st, bf.a_in, kin_ld, M, in_proj, e);
-  cast_mask<T>(st, bf.hproj, (T*)bf.c_in, batches, N, d, lens_conv);
+  e.addend = bf.hconst;
+  e.ld_add = d;
+  simt_gemm(st, bf.a_in, kin_ld, M, in_proj.f32, kin, d, a.mel_dim, e);
+  // bf16 mode feeds the position-embedding conv IEEE fp16 operands (kind::f16 runs both formats at the same rate):
+  // h carries the large, slowly varying cond/text offsets and loses too much in 8 mantissa bits (precision)
+  if (is16) cast_mask<__half>(st, bf.hproj, (__half*)bf.c_in, batches, N, d, lens_conv);
+  else cast_mask<float>(st, bf.hproj, (float*)bf.c_in, batches, N, d, lens_conv);
   float* dst = is_dit ? bf.x : bf.y /*unused*/;
   (void)dst;
   for (int c = 0; c < 2; ++c) {
@@ -415,19 +440,19 @@ void f5b_plan::input_embed(cudaStream_t st, int batches, int N, const int* lens_
     const void* src = c == 0 ? bf.c_in : bf.c_mid;
     if (c == 0) {
       ec.out = bf.c_mid;
-      ec.out_bf16 = is16;
+      ec.out_type = is16 ? OUT_F16 : OUT_F32;
       ec.ldo = d;
     } else {
       // x = mish(conv) + h.  DiT: straight into the residual stream; UNetT: into bf.norm-sized fp32 scratch (bf.v? no)
       ec.out = is_dit ? (void*)bf.x : (void*)bf.skips[0];
-      ec.out_bf16 = 0;
+      ec.out_type = 0;
       ec.ldo = d;
       ec.addend = bf.hproj;
       ec.ld_add = d;
     }
     if (is16) {
-      TcConv cv{31, 15, d / 16, d};
-      tc_gemm(st, ctx.sm_count, (const bf16*)src, d, N, batches, conv_w16[c], (long long)31 * (d / 16), d,
+      TcConv cv{31, 15, d / 16, d, 1};
+      tc_gemm(st, ctx.sm_count, (const bf16*)src, d, N, batches, (const bf16*)conv_w16[c], (long long)31 * (d / 16), d,
               31 * (d / 16), ec, &cv, 0);
     } else {
       simt_group_conv(st, (const float*)src, batches, N, d, conv_w_r[c], 31, 15, 16, ec);
@@ -482,7 +507,7 @@ void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int
     EpiParams eq;
     eq.bias = L.bqkv;
     eq.out = bf.qkv;
-    eq.out_bf16 = is16;
+    eq.out_type = is16;
     eq.ldo = 3 * inner;
     eq.n_valid = 3 * inner;
     eq.rows_per_batch = R;
@@ -518,7 +543,7 @@ void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int
     e1.act = ACT_GELU_TANH;
     e1.bias = L.bff1;
     e1.out = bf.ffh;
-    e1.out_bf16 = is16;
+    e1.out_type = is16;
     e1.ldo = ffd;
     e1.n_valid = ffd;
     run_gemm(ctx, st, bf.norm, d, M, L.ff1, e1);
@@ -544,12 +569,15 @@ void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int
   ep.rows_per_batch = R;
   if (is_dit) {
     const float* fin = bf.ada + (long long)tbl_row * ada_W + (long long)a.depth * 6 * d;  // (scale, shift)
-    ln_mod<T>(st, bf.x, (T*)bf.norm, M, d, fin, fin + d, 1.0f, tb_stride, R, tbl_bmod, 1e-6f);
+    if (is16) ln_mod<bf16x3>(st, bf.x, (bf16x3*)bf.norm3, M, d, fin, fin + d, 1.0f, tb_stride, R, tbl_bmod, 1e-6f);
+    else ln_mod<T>(st, bf.x, (T*)bf.norm, M, d, fin, fin + d, 1.0f, tb_stride, R, tbl_bmod, 1e-6f);
   } else {
-    xrms_norm<T>(st, bf.x, (T*)bf.norm, M, d, norm_out_g);
+    if (is16) xrms_norm<bf16x3>(st, bf.x, (bf16x3*)bf.norm3, M, d, norm_out_g);
+    else xrms_norm<T>(st, bf.x, (T*)bf.norm, M, d, norm_out_g);
     ep.row_skip = 1;  // norm_out(x)[:, 1:, :]
   }
-  run_gemm(ctx, st, bf.norm, d, M, proj_out, ep, 64);
+  if (is16) run_gemm(ctx, st, bf.norm3, 3 * d, M, proj_out, ep, 64);
+  else run_gemm(ctx, st, bf.norm, d, M, proj_out, ep, 64);
 }
 
 #include "backbone_api.inc"

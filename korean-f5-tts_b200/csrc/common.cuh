@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cstdint>
 #include <cstdio>
 #include <string>
@@ -58,12 +59,13 @@ long long last_call();
 // epilogue shared by the SIMT (fp32) and tcgen05 (bf16) GEMMs
 // ---------------------------------------------------------------------------------------------
 enum : int { EPI_STORE = 0, EPI_RESID = 1 };
+enum : int { OUT_F32 = 0, OUT_BF16 = 1, OUT_F16 = 2 };
 enum : int { ACT_NONE = 0, ACT_GELU_TANH = 1, ACT_GELU_ERF = 2, ACT_MISH = 3, ACT_SILU = 4 };
 
 struct EpiParams {
   int kind = EPI_STORE;
   int act = ACT_NONE;
-  int out_bf16 = 0;               // STORE target element type
+  int out_type = 0;               // STORE target element type: OUT_F32 / OUT_BF16 / OUT_F16
   int n_valid = 0;                // columns >= n_valid are dropped
   const float* bias = nullptr;    // [N] or null
   void* out = nullptr;            // STORE: out[m*ldo + n] = act(v) (+ addend)
@@ -111,6 +113,11 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+__device__ __forceinline__ uint32_t pack_f16x2(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -126,6 +133,7 @@ __device__ __forceinline__ float ld_as_float(const float* p) { return *p; }
 __device__ __forceinline__ float ld_as_float(const bf16* p) { return __bfloat162float(*p); }
 __device__ __forceinline__ void st_from_float(float* p, float v) { *p = v; }
 __device__ __forceinline__ void st_from_float(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
+__device__ __forceinline__ void st_from_float(__half* p, float v) { *p = __float2half_rn(v); }
 
 // Apply the epilogue to NC (multiple of 4) consecutive accumulator columns [n0, n0+NC) of global row m.
 // n0 must be a multiple of 4 (RoPE pairs and the vector stores rely on it).
@@ -215,7 +223,7 @@ __device__ __forceinline__ void epi_apply(const EpiParams& p, long long m, int n
       }
     }
   }
-  if (p.out_bf16) {
+  if (p.out_type == OUT_BF16) {
     bf16* o = reinterpret_cast<bf16*>(p.out) + mo * p.ldo + n0;
 #pragma unroll
     for (int j = 0; j < NC; j += 4) {
@@ -228,6 +236,21 @@ __device__ __forceinline__ void epi_apply(const EpiParams& p, long long m, int n
 #pragma unroll
         for (int q = 0; q < 4; ++q)
           if (n0 + j + q < p.n_valid) o[j + q] = __float2bfloat16_rn(v[j + q]);
+      }
+    }
+  } else if (p.out_type == OUT_F16) {
+    __half* o = reinterpret_cast<__half*>(p.out) + mo * p.ldo + n0;
+#pragma unroll
+    for (int j = 0; j < NC; j += 4) {
+      if (n0 + j + 4 <= p.n_valid) {
+        uint2 pk;
+        pk.x = pack_f16x2(v[j], v[j + 1]);
+        pk.y = pack_f16x2(v[j + 2], v[j + 3]);
+        *reinterpret_cast<uint2*>(o + j) = pk;
+      } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (n0 + j + q < p.n_valid) o[j + q] = __float2half_rn(v[j + q]);
       }
     }
   } else {

@@ -56,6 +56,7 @@ class WeightStore {
 void run_gemm(const DeviceCtx& ctx, cudaStream_t st, const void* A, long long lda, long long M, const WMat& w,
               const EpiParams& ep, int force_bn = 0);
 WMat make_wmat(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K);
+WMat make_wmat_split3(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K);
 // cat rows of several [Ni, K] fp32 matrices into one device matrix
 float* concat_rows(Arena* arena, cudaStream_t st, const std::vector<std::pair<const float*, long long>>& parts);
 

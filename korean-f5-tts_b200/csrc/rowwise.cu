@@ -19,6 +19,13 @@ __device__ __forceinline__ void store4<bf16>(bf16* p, float a, float b, float c,
   pk.y = pack_bf16x2(c, d);
   *reinterpret_cast<uint2*>(p) = pk;
 }
+template <>
+__device__ __forceinline__ void store4<__half>(__half* p, float a, float b, float c, float d) {
+  uint2 pk;
+  pk.x = pack_f16x2(a, b);
+  pk.y = pack_f16x2(c, d);
+  *reinterpret_cast<uint2*>(p) = pk;
+}
 template <typename T>
 __device__ __forceinline__ float4 load4(const T* p);
 template <>
@@ -33,6 +40,31 @@ __device__ __forceinline__ float4 load4<bf16>(const bf16* p) {
   float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
   return make_float4(fa.x, fa.y, fb.x, fb.y);
 }
+
+template <typename T>
+struct RowOut {
+  static constexpr int kWidth = 1;
+  static __device__ __forceinline__ void st(T* row, int c, int d, float a, float b, float cc, float dd) {
+    store4<T>(row + c, a, b, cc, dd);
+  }
+};
+template <>
+struct RowOut<bf16x3> {
+  static constexpr int kWidth = 3;
+  static __device__ __forceinline__ void st(bf16x3* row, int c, int d, float a, float b, float cc, float dd) {
+    bf16* r = reinterpret_cast<bf16*>(row);
+    const float v[4] = {a, b, cc, dd};
+    float hi[4], lo[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      hi[i] = __bfloat162float(__float2bfloat16_rn(v[i]));
+      lo[i] = v[i] - hi[i];
+    }
+    store4<bf16>(r + c, hi[0], hi[1], hi[2], hi[3]);
+    store4<bf16>(r + d + c, lo[0], lo[1], lo[2], lo[3]);
+    store4<bf16>(r + 2 * d + c, hi[0], hi[1], hi[2], hi[3]);
+  }
+};
 
 // ---------------------------------------------------------------------------------------------
 // LayerNorm (no affine) + modulation / affine
@@ -62,14 +94,14 @@ ln_mod_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int
   const int b = (int)((m / rows_per_batch) % bmod);
   const float* mu = mul ? mul + b * vec_bstride : nullptr;
   const float* ad = add ? add + b * vec_bstride : nullptr;
-  T* orow = out + m * d;
+  T* orow = out + m * d * RowOut<T>::kWidth;
   for (int c = lane * 4; c < d; c += 128) {
     float4 v = *reinterpret_cast<const float4*>(xr + c);
     float4 g = mu ? __ldg(reinterpret_cast<const float4*>(mu + c)) : make_float4(0, 0, 0, 0);
     float4 h = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
     if (!mu) g = make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
-    store4<T>(orow + c, (v.x - mean) * rstd * (mul_off + g.x) + h.x, (v.y - mean) * rstd * (mul_off + g.y) + h.y,
-              (v.z - mean) * rstd * (mul_off + g.z) + h.z, (v.w - mean) * rstd * (mul_off + g.w) + h.w);
+    RowOut<T>::st(orow, c, d, (v.x - mean) * rstd * (mul_off + g.x) + h.x, (v.y - mean) * rstd * (mul_off + g.y) + h.y,
+                  (v.z - mean) * rstd * (mul_off + g.z) + h.z, (v.w - mean) * rstd * (mul_off + g.w) + h.w);
   }
 }
 
@@ -85,6 +117,8 @@ template void ln_mod<float>(cudaStream_t, const float*, float*, long long, int, 
                             long long, int, int, float);
 template void ln_mod<bf16>(cudaStream_t, const float*, bf16*, long long, int, const float*, const float*, float,
                            long long, int, int, float);
+template void ln_mod<bf16x3>(cudaStream_t, const float*, bf16x3*, long long, int, const float*, const float*, float,
+                             long long, int, int, float);
 
 // ---------------------------------------------------------------------------------------------
 // x_transformers RMSNorm
@@ -104,11 +138,11 @@ xrms_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d
   }
   const float nrm = fmaxf(sqrtf(warp_sum(q)), 1e-12f);
   const float sc = sqrt_d / nrm;
-  T* orow = out + m * d;
+  T* orow = out + m * d * RowOut<T>::kWidth;
   for (int c = lane * 4; c < d; c += 128) {
     float4 v = *reinterpret_cast<const float4*>(xr + c);
     float4 gg = __ldg(reinterpret_cast<const float4*>(g + c));
-    store4<T>(orow + c, v.x * sc * gg.x, v.y * sc * gg.y, v.z * sc * gg.z, v.w * sc * gg.w);
+    RowOut<T>::st(orow, c, d, v.x * sc * gg.x, v.y * sc * gg.y, v.z * sc * gg.z, v.w * sc * gg.w);
   }
 }
 template <typename T>
@@ -119,6 +153,7 @@ void xrms_norm(cudaStream_t st, const float* x, T* out, long long M, int d, cons
 }
 template void xrms_norm<float>(cudaStream_t, const float*, float*, long long, int, const float*);
 template void xrms_norm<bf16>(cudaStream_t, const float*, bf16*, long long, int, const float*);
+template void xrms_norm<bf16x3>(cudaStream_t, const float*, bf16x3*, long long, int, const float*);
 
 // ---------------------------------------------------------------------------------------------
 // depthwise conv k7 + bias + LayerNorm(affine): one warp per output row, <= 32 channels per lane
@@ -325,36 +360,31 @@ void mask_rows(cudaStream_t st, float* x, long long M, int d, const unsigned cha
 // ---------------------------------------------------------------------------------------------
 // sampler glue: A_in assembly, CFG combine + Euler update, masks, tables
 // ---------------------------------------------------------------------------------------------
-template <typename T>
 __global__ void __launch_bounds__(256)
-build_a_in_kernel(T* __restrict__ a_in, long long ld, int B, int batches, int rows, int mel, int td,
+build_a_in_kernel(float* __restrict__ a_in, long long ld, int B, int batches, int rows, int mel, int td,
                   const float* __restrict__ cond, const float* __restrict__ text_emb, int uncond_from) {
   const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (m >= (long long)batches * rows) return;
   const int b2 = (int)(m / rows), pos = (int)(m - (long long)b2 * rows);
   const int b = b2 % B;
-  T* row = a_in + m * ld;
+  float* row = a_in + m * ld;
   const float* cr = cond + ((long long)b * rows + pos) * mel;
   const bool drop = b2 >= uncond_from;
   for (int c = lane; c < mel; c += 32) st_from_float(row + mel + c, drop ? 0.0f : cr[c]);
   const float* tr = text_emb + m * td;
   for (int c = lane; c < td; c += 32) st_from_float(row + 2 * mel + c, tr[c]);
 }
-template <typename T>
-void build_a_in(cudaStream_t st, T* a_in, long long ld, int B, int batches, int rows, int mel, int td,
+void build_a_in(cudaStream_t st, float* a_in, long long ld, int B, int batches, int rows, int mel, int td,
                 const float* cond, const float* text_emb, int uncond_from) {
-  build_a_in_kernel<T><<<ceil_div_ll((long long)batches * rows, 8), 256, 0, st>>>(a_in, ld, B, batches, rows, mel, td,
+  build_a_in_kernel<<<ceil_div_ll((long long)batches * rows, 8), 256, 0, st>>>(a_in, ld, B, batches, rows, mel, td,
                                                                                  cond, text_emb, uncond_from);
   F5B_POST_LAUNCH();
 }
-template void build_a_in<float>(cudaStream_t, float*, long long, int, int, int, int, int, const float*, const float*, int);
-template void build_a_in<bf16>(cudaStream_t, bf16*, long long, int, int, int, int, int, const float*, const float*, int);
 
 // v [branches*B*rows, mel]: branch 0 = cond prediction, branch 1 = uncond.  dt == 0 with v == null just scatters y.
-template <typename T>
 __global__ void __launch_bounds__(256)
-cfg_euler_kernel(float* __restrict__ y, const float* __restrict__ v, T* __restrict__ a_in, long long ld, int B,
+cfg_euler_kernel(float* __restrict__ y, const float* __restrict__ v, float* __restrict__ a_in, long long ld, int B,
                  int branches, int rows, int mel, float dt, float cfg, float* __restrict__ traj, long long total) {
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= total) return;
@@ -375,16 +405,13 @@ cfg_euler_kernel(float* __restrict__ y, const float* __restrict__ v, T* __restri
   st_from_float(a_in + m * ld + c, yv);
   if (branches == 2) st_from_float(a_in + (m + (long long)B * rows) * ld + c, yv);
 }
-template <typename T>
-void cfg_euler(cudaStream_t st, float* y, const float* v, T* a_in, long long ld, int B, int branches, int rows,
+void cfg_euler(cudaStream_t st, float* y, const float* v, float* a_in, long long ld, int B, int branches, int rows,
                int mel, float dt, float cfg, float* traj_slot) {
   long long total = (long long)B * rows * mel;
-  cfg_euler_kernel<T><<<ceil_div_ll(total, 256), 256, 0, st>>>(y, v, a_in, ld, B, branches, rows, mel, dt, cfg,
+  cfg_euler_kernel<<<ceil_div_ll(total, 256), 256, 0, st>>>(y, v, a_in, ld, B, branches, rows, mel, dt, cfg,
                                                                traj_slot, total);
   F5B_POST_LAUNCH();
 }
-template void cfg_euler<float>(cudaStream_t, float*, const float*, float*, long long, int, int, int, int, float, float, float*);
-template void cfg_euler<bf16>(cudaStream_t, float*, const float*, bf16*, long long, int, int, int, int, float, float, float*);
 
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -408,6 +435,7 @@ void cast_mask(cudaStream_t st, const float* x, T* out, int batches, int rows, i
 }
 template void cast_mask<float>(cudaStream_t, const float*, float*, int, int, int, const int*);
 template void cast_mask<bf16>(cudaStream_t, const float*, bf16*, int, int, int, const int*);
+template void cast_mask<__half>(cudaStream_t, const float*, __half*, int, int, int, const int*);
 
 __global__ void rope_table_kernel(float* __restrict__ cs, int rows, const float* __restrict__ inv_freq) {
   const int i = blockIdx.x * 256 + threadIdx.x;

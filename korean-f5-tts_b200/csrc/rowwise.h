@@ -5,6 +5,11 @@
 
 namespace f5b {
 
+// Output tag for the precise bf16 contraction of proj_out: a row of width d is written as three bf16 segments
+// [hi | lo | hi] (hi = bf16(v), lo = bf16(v - hi)), to be contracted with weights laid out [W_hi | W_hi | W_lo]:
+// sum = hi*W_hi + lo*W_hi + hi*W_lo, i.e. ~16 mantissa bits on both operands at 3x the (tiny) K.
+struct bf16x3 { bf16 raw; };
+
 // out[m, :] = LN(x[m, :], eps) * (mul_off + mul[b, :]) + add[b, :]      (reference modules.py:307-342, 256-259)
 //   b = (m / rows_per_batch) % bmod; mul/add may be null (-> 1 / 0).
 template <typename T>
@@ -34,12 +39,10 @@ void text_lookup(cudaStream_t st, const long long* text, int B, int nt, int bran
 void mask_rows(cudaStream_t st, float* x, long long M, int d, const unsigned char* keep);
 
 // A_in[m, 100:200) = cond (zero for the uncond branch), A_in[m, 200:200+td) = text embedding.
-template <typename T>
-void build_a_in(cudaStream_t st, T* a_in, long long ld, int B, int batches, int rows, int mel, int td,
+void build_a_in(cudaStream_t st, float* a_in, long long ld, int B, int batches, int rows, int mel, int td,
                 const float* cond, const float* text_emb, int uncond_from);
 // y (+)= ...; also scatters y into the x columns of A_in for every branch and, optionally, into the trajectory.
-template <typename T>
-void cfg_euler(cudaStream_t st, float* y, const float* v, T* a_in, long long ld, int B, int branches, int rows,
+void cfg_euler(cudaStream_t st, float* y, const float* v, float* a_in, long long ld, int B, int branches, int rows,
                int mel, float dt, float cfg, float* traj_slot);
 
 template <typename T>

@@ -88,6 +88,40 @@ WMat make_wmat(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float*
   return m;
 }
 
+__global__ void split3_weight_kernel(const float* __restrict__ in, bf16* __restrict__ out, int K, long long total) {
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  long long r = i / K;
+  int c = (int)(i - r * K);
+  float v = in[i];
+  bf16 hi = __float2bfloat16_rn(v);
+  bf16 lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+  bf16* o = out + r * 3 * K;
+  o[c] = hi;
+  o[K + c] = hi;
+  o[2 * K + c] = lo;
+}
+
+// [N, K] fp32 -> bf16 [N, 3K] = [W_hi | W_hi | W_lo], the partner of the bf16x3 activation layout (rowwise.h).
+WMat make_wmat_split3(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K) {
+  WMat m;
+  m.f32 = w32;
+  m.N = N;
+  m.K = K;
+  m.ld32 = K;
+  if (ctx.mode == F5B_MODE_BF16) {
+    F5B_REQUIRE(K % 8 == 0, "split3 weights need K % 8 == 0");
+    bf16* p = arena->alloc_n<bf16>((size_t)N * 3 * K);
+    long long total = (long long)N * K;
+    split3_weight_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(w32, p, K, total);
+    F5B_POST_LAUNCH();
+    m.b16 = p;
+    m.ld16 = 3LL * K;
+    m.K = 3 * K;
+  }
+  return m;
+}
+
 float* concat_rows(Arena* arena, cudaStream_t st, const std::vector<std::pair<const float*, long long>>& parts) {
   long long total = 0;
   for (auto& p : parts) total += p.second;
@@ -264,7 +298,7 @@ int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, f
     F5B_CHECK_CUDA(cudaMemsetAsync(W, 0x3c, (size_t)N * ld * 2, st));
     EpiParams ep;
     ep.out = O;
-    ep.out_bf16 = 1;
+    ep.out_type = 1;
     ep.ldo = N;
     ep.n_valid = N;
     timed([&] { tc_gemm(st, ctx.sm_count, A, ld, M, 1, W, ld, N, K, ep, nullptr, 0); });

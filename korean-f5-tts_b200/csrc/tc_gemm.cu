@@ -33,7 +33,6 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   constexpr int B_STAGE_BYTES = BN * BK * 2;
   constexpr uint32_t STAGE_TX = A_STAGE_BYTES + B_STAGE_BYTES;
   constexpr uint32_t ACC_COLS = 2 * BN;
-  constexpr uint32_t IDESC = umma_idesc_bf16(BM, BN, 0, 0);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -109,7 +108,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int k = 0; k < BK / 16; ++k) {
           const uint64_t ad = umma_desc_sw128(a_addr + k * 32, 16, 1024);
           const uint64_t bd = umma_desc_sw128(b_addr + k * 32, 16, 1024);
-          umma_ss(d_tmem, ad, bd, IDESC, (kb | k) != 0 ? 1u : 0u);
+          umma_ss(d_tmem, ad, bd, s.idesc, (kb | k) != 0 ? 1u : 0u);
         }
         umma_commit(&empty[st]);  // frees the smem slot once these MMAs have read it
       }
@@ -168,7 +167,7 @@ static void load_encode() {
 }
 
 void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                    const uint32_t* box) {
+                    const uint32_t* box, int fp16) {
   load_encode();
   F5B_REQUIRE(g_encode != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver)");
   F5B_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
@@ -184,7 +183,7 @@ void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t
     gs[i] = strides_bytes[i];
     F5B_REQUIRE(gs[i] % 16 == 0, "TMA strides must be multiples of 16 bytes");
   }
-  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx,
+  CUresult r = g_encode(out, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx,
                         es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -257,19 +256,21 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
   }
   s.tiles_n = (N + bn - 1) / bn;
   s.num_kb = (K + BK - 1) / BK;
+  const int fp16 = conv != nullptr && conv->fp16;
+  s.idesc = fp16 ? umma_idesc_f16(BM, bn, 0, 0) : umma_idesc_bf16(BM, bn, 0, 0);
 
   CUtensorMap ta, tb;
   {
     uint64_t dims[3] = {(uint64_t)a_cols, (uint64_t)rows_per_batch, (uint64_t)batches};
     uint64_t strides[2] = {(uint64_t)lda * 2, (uint64_t)lda * 2 * (uint64_t)rows_per_batch};
     uint32_t box[3] = {BK, BM, 1};
-    make_tmap_bf16(&ta, A, 3, dims, strides, box);
+    make_tmap_bf16(&ta, A, 3, dims, strides, box, fp16);
   }
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)N};
     uint64_t strides[1] = {(uint64_t)ldw * 2};
     uint32_t box[2] = {BK, (uint32_t)bn};
-    make_tmap_bf16(&tb, W, 2, dims, strides, box);
+    make_tmap_bf16(&tb, W, 2, dims, strides, box, fp16);
   }
   long long total = (long long)s.tiles_m_per_batch * batches * s.tiles_n;
   int grid = (int)(total < sm_count ? total : sm_count);

@@ -16,6 +16,7 @@ struct TcGemmShape {
   int conv_kb_per_tap;
   int conv_pad;
   int conv_cg;
+  unsigned idesc;  // tcgen05 instruction descriptor (operand formats differ between the bf16 and fp16 variants)
 };
 
 // Grouped 1-D convolution expressed as a GEMM: K index = tap * cg + ci, A column = group * cg + ci,
@@ -25,10 +26,11 @@ struct TcConv {
   int pad;       // 15
   int cg;        // channels per group
   int channels;  // total input channels (width of A)
+  int fp16;      // operands are IEEE fp16 instead of bf16 (same tensor-core rate, 3 more mantissa bits)
 };
 
 void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                    const uint32_t* box);
+                    const uint32_t* box, int fp16 = 0);
 
 // bf16 tensor-core GEMM: out = epilogue(A[rows, K] * W[N, K]^T).  A rows are [batches][rows_per_batch] with a
 // common leading dimension lda (elements).

@@ -126,7 +126,7 @@ struct f5b_vocos {
       e1.act = ACT_GELU_ERF;
       e1.bias = b.b1;
       e1.out = h;
-      e1.out_bf16 = is16;
+      e1.out_type = is16;
       e1.ldo = V_INT;
       e1.n_valid = V_INT;
       run_gemm(ctx, st, norm, V_DIM, M, b.pw1, e1);

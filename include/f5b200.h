@@ -104,7 +104,7 @@ int f5b_op_gemm(int32_t mode, const float* A, const float* W, const float* bias,
 int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int32_t batches, int32_t rows,
                      int32_t heads, float* out, int32_t device, void* stream);
 /* Times `iters` back-to-back launches of one kernel with CUDA events on `stream`; returns average ms in *ms.
- *   which: 0 = bf16 tcgen05 GEMM [M,K]x[N,K], 1 = bf16 tcgen05 attention (M = rows, N = heads, K = batches),
+ *   which: 0 = bf16 tcgen05 GEMM [M,K]x[N,K] (64/128/256: forced tile width; 4: gate*y+residual epilogue), 1 = bf16 tcgen05 attention (M = rows, N = heads, K = batches),
  *          2 = LN+modulate (M rows, N = dim). */
 int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, float* ms, int32_t device, void* stream);
 

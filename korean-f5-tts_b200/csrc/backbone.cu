@@ -426,10 +426,9 @@ void f5b_plan::input_embed(cudaStream_t st, int batches, int N, const int* lens_
   simt_gemm(st, bf.a_in, kin_ld, M, in_proj.f32, kin, d, a.mel_dim, e);
   // bf16 mode feeds the position-embedding conv IEEE fp16 operands (kind::f16 runs both formats at the same rate):
   // h carries the large, slowly varying cond/text offsets and loses too much in 8 mantissa bits (precision)
-  if (is16) cast_mask<__half>(st, bf.hproj, (__half*)bf.c_in, batches, N, d, lens_conv);
+  float* xdst = is_dit ? bf.x : bf.skips[0];
+  if (is16) cast_mask<__half>(st, bf.hproj, (__half*)bf.c_in, batches, N, d, lens_conv, xdst);  // xdst = h
   else cast_mask<float>(st, bf.hproj, (float*)bf.c_in, batches, N, d, lens_conv);
-  float* dst = is_dit ? bf.x : bf.y /*unused*/;
-  (void)dst;
   for (int c = 0; c < 2; ++c) {
     EpiParams ec;
     ec.act = ACT_MISH;
@@ -442,10 +441,14 @@ void f5b_plan::input_embed(cudaStream_t st, int batches, int N, const int* lens_
       ec.out = bf.c_mid;
       ec.out_type = is16 ? OUT_F16 : OUT_F32;
       ec.ldo = d;
+    } else if (is16) {
+      // x = h + mish(conv): xdst already holds h, the tensor-core epilogue adds the conv branch (TMA reduce-add)
+      ec.kind = EPI_RESID;
+      ec.resid = xdst;
+      ec.ldr = d;
     } else {
-      // x = mish(conv) + h.  DiT: straight into the residual stream; UNetT: into bf.norm-sized fp32 scratch (bf.v? no)
-      ec.out = is_dit ? (void*)bf.x : (void*)bf.skips[0];
-      ec.out_type = 0;
+      ec.out = xdst;
+      ec.out_type = OUT_F32;
       ec.ldo = d;
       ec.addend = bf.hproj;
       ec.ld_add = d;

@@ -105,12 +105,65 @@ ln_mod_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int
   }
 }
 
+// Register-resident variant for d <= 1024: the row is read from memory once (8 float4 per lane).
+template <typename T>
+__global__ void __launch_bounds__(256)
+ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d, const float* __restrict__ mul,
+                  const float* __restrict__ add, float mul_off, long long vec_bstride, int rows_per_batch, int bmod,
+                  float eps) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= M) return;
+  const float* xr = x + m * d;
+  float4 buf[8];
+  float s = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < d) {
+      buf[i] = *reinterpret_cast<const float4*>(xr + c);
+      s += (buf[i].x + buf[i].y) + (buf[i].z + buf[i].w);
+    }
+  }
+  const float mean = warp_sum(s) / d;
+  float q = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < d) {
+      float a = buf[i].x - mean, b = buf[i].y - mean, cc = buf[i].z - mean, dd = buf[i].w - mean;
+      q += (a * a + b * b) + (cc * cc + dd * dd);
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / d + eps);
+  const int b = (int)((m / rows_per_batch) % bmod);
+  const float* mu = mul ? mul + b * vec_bstride : nullptr;
+  const float* ad = add ? add + b * vec_bstride : nullptr;
+  T* orow = out + m * d * RowOut<T>::kWidth;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < d) {
+      const float4 v = buf[i];
+      float4 g = mu ? __ldg(reinterpret_cast<const float4*>(mu + c)) : make_float4(0, 0, 0, 0);
+      float4 h = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
+      if (!mu) g = make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
+      RowOut<T>::st(orow, c, d, (v.x - mean) * rstd * (mul_off + g.x) + h.x, (v.y - mean) * rstd * (mul_off + g.y) + h.y,
+                    (v.z - mean) * rstd * (mul_off + g.z) + h.z, (v.w - mean) * rstd * (mul_off + g.w) + h.w);
+    }
+  }
+}
+
 template <typename T>
 void ln_mod(cudaStream_t st, const float* x, T* out, long long M, int d, const float* mul, const float* add,
             float mul_off, long long vec_bstride, int rows_per_batch, int bmod, float eps) {
   F5B_REQUIRE(d % 4 == 0, "LayerNorm width must be a multiple of 4");
-  ln_mod_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride, rows_per_batch,
-                                                      bmod < 1 ? 1 : bmod, eps);
+  if (d <= 1024)
+    ln_mod_reg_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride,
+                                                            rows_per_batch, bmod < 1 ? 1 : bmod, eps);
+  else
+    ln_mod_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride, rows_per_batch,
+                                                        bmod < 1 ? 1 : bmod, eps);
   F5B_POST_LAUNCH();
 }
 template void ln_mod<float>(cudaStream_t, const float*, float*, long long, int, const float*, const float*, float,
@@ -416,11 +469,12 @@ void cfg_euler(cudaStream_t st, float* y, const float* v, float* a_in, long long
 template <typename T>
 __global__ void __launch_bounds__(256)
 cast_mask_kernel(const float* __restrict__ x, T* __restrict__ out, int rows, int d4, const int* __restrict__ row_len,
-                 long long total4) {
+                 long long total4, float* __restrict__ copy) {
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= total4) return;
   const long long m = i / d4;
   float4 v = reinterpret_cast<const float4*>(x)[i];
+  if (copy) reinterpret_cast<float4*>(copy)[i] = v;
   if (row_len) {
     const int b = (int)(m / rows), pos = (int)(m - (long long)b * rows);
     if (pos >= row_len[b]) v = make_float4(0, 0, 0, 0);
@@ -428,14 +482,14 @@ cast_mask_kernel(const float* __restrict__ x, T* __restrict__ out, int rows, int
   store4<T>(out + i * 4, v.x, v.y, v.z, v.w);
 }
 template <typename T>
-void cast_mask(cudaStream_t st, const float* x, T* out, int batches, int rows, int d, const int* row_len) {
+void cast_mask(cudaStream_t st, const float* x, T* out, int batches, int rows, int d, const int* row_len, float* copy) {
   long long total4 = (long long)batches * rows * d / 4;
-  cast_mask_kernel<T><<<ceil_div_ll(total4, 256), 256, 0, st>>>(x, out, rows, d / 4, row_len, total4);
+  cast_mask_kernel<T><<<ceil_div_ll(total4, 256), 256, 0, st>>>(x, out, rows, d / 4, row_len, total4, copy);
   F5B_POST_LAUNCH();
 }
-template void cast_mask<float>(cudaStream_t, const float*, float*, int, int, int, const int*);
-template void cast_mask<bf16>(cudaStream_t, const float*, bf16*, int, int, int, const int*);
-template void cast_mask<__half>(cudaStream_t, const float*, __half*, int, int, int, const int*);
+template void cast_mask<float>(cudaStream_t, const float*, float*, int, int, int, const int*, float*);
+template void cast_mask<bf16>(cudaStream_t, const float*, bf16*, int, int, int, const int*, float*);
+template void cast_mask<__half>(cudaStream_t, const float*, __half*, int, int, int, const int*, float*);
 
 __global__ void rope_table_kernel(float* __restrict__ cs, int rows, const float* __restrict__ inv_freq) {
   const int i = blockIdx.x * 256 + threadIdx.x;

@@ -45,8 +45,10 @@ void build_a_in(cudaStream_t st, float* a_in, long long ld, int B, int batches, 
 void cfg_euler(cudaStream_t st, float* y, const float* v, float* a_in, long long ld, int B, int branches, int rows,
                int mel, float dt, float cfg, float* traj_slot);
 
+// out = masked cast of x; copy (optional) = x unchanged (seeds the residual stream for the conv pos-emb epilogue)
 template <typename T>
-void cast_mask(cudaStream_t st, const float* x, T* out, int batches, int rows, int d, const int* row_len);
+void cast_mask(cudaStream_t st, const float* x, T* out, int batches, int rows, int d, const int* row_len,
+               float* copy = nullptr);
 
 void rope_table(cudaStream_t st, float* cs, int rows, const float* inv_freq32);
 void sinus_time(cudaStream_t st, const float* t, int n, const float* freq128, float* out /* [n,256] */);

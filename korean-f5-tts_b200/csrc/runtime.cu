@@ -139,7 +139,13 @@ void run_gemm(const DeviceCtx& ctx, cudaStream_t st, const void* A, long long ld
   if (ctx.mode == F5B_MODE_BF16) {
     F5B_REQUIRE(w.b16 != nullptr, "bf16 weight missing");
     F5B_REQUIRE(M < (1LL << 31), "GEMM rows overflow");
-    tc_gemm(st, ctx.sm_count, reinterpret_cast<const bf16*>(A), lda, (int)M, 1, w.b16, w.ld16, w.N, w.K, ep, nullptr,
+    int rpb = (int)M, nb = 1;
+    if (ep.row_skip > 0) {  // dropped leading rows are expressed as a TMA coordinate shift per batch element
+      F5B_REQUIRE(M % ep.rows_per_batch == 0, "row_skip needs whole batch elements");
+      rpb = ep.rows_per_batch;
+      nb = (int)(M / ep.rows_per_batch);
+    }
+    tc_gemm(st, ctx.sm_count, reinterpret_cast<const bf16*>(A), lda, rpb, nb, w.b16, w.ld16, w.N, w.K, ep, nullptr,
             force_bn);
   } else {
     simt_gemm(st, reinterpret_cast<const float*>(A), lda, M, w.f32, w.ld32, w.N, w.K, ep);
@@ -279,29 +285,68 @@ int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, f
   cudaEvent_t e0, e1;
   F5B_CHECK_CUDA(cudaEventCreate(&e0));
   F5B_CHECK_CUDA(cudaEventCreate(&e1));
+  // `iters` launches are captured into one CUDA graph and the graph is timed: host launch cost (three tensor-map
+  // encodes per GEMM) would otherwise bound kernels of a few microseconds
+  cudaStream_t cs = nullptr;
+  F5B_CHECK_CUDA(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+  cudaStream_t user_st = st;
+  st = cs;
   auto timed = [&](auto&& fn) {
-    for (int i = 0; i < 3; ++i) fn();
-    F5B_CHECK_CUDA(cudaEventRecord(e0, st));
+    fn();
+    F5B_CHECK_CUDA(cudaStreamSynchronize(cs));
+    cudaGraph_t g = nullptr;
+    cudaGraphExec_t ge = nullptr;
+    long long c0 = launch_count();
+    F5B_CHECK_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
     for (int i = 0; i < iters; ++i) fn();
-    F5B_CHECK_CUDA(cudaEventRecord(e1, st));
+    F5B_CHECK_CUDA(cudaStreamEndCapture(cs, &g));
+    count_launch(-(launch_count() - c0));
+    F5B_CHECK_CUDA(cudaGraphInstantiate(&ge, g, 0));
+    F5B_CHECK_CUDA(cudaStreamSynchronize(user_st));
+    F5B_CHECK_CUDA(cudaGraphLaunch(ge, cs));  // warm-up replay
+    F5B_CHECK_CUDA(cudaEventRecord(e0, cs));
+    F5B_CHECK_CUDA(cudaGraphLaunch(ge, cs));
+    F5B_CHECK_CUDA(cudaEventRecord(e1, cs));
     F5B_CHECK_CUDA(cudaEventSynchronize(e1));
+    count_launch(2LL * iters);
     float t = 0;
     F5B_CHECK_CUDA(cudaEventElapsedTime(&t, e0, e1));
     *ms = t / iters;
+    cudaGraphExecDestroy(ge);
+    cudaGraphDestroy(g);
   };
-  if (which == 0) {
+  if (which == 0 || which == 4 || which == 5 || which == 6 || which == 64 || which == 128 || which == 256) {
+    // 0: bf16 store, tile width chosen by the library; 64/128/256: forced tile width; 4: gate*y + residual (fp32 reduce)
     long long ld = (K + 7) / 8 * 8;
     bf16* A = arena.alloc_n<bf16>((size_t)M * ld);
-    bf16* W = arena.alloc_n<bf16>((size_t)N * ld);
+    // in the sampling loop every GEMM streams its weights from HBM (0.66 GB per evaluation > 126 MB L2): rotate over
+    // enough weight copies that none is L2-resident when its turn comes again
+    const size_t wbytes = (size_t)N * ld * 2;
+    int ncopy = (int)((size_t)(192u << 20) / wbytes) + 1;
+    if (ncopy > iters) ncopy = iters;
+    bf16* W = arena.alloc_n<bf16>((size_t)N * ld * ncopy);
     bf16* O = arena.alloc_n<bf16>((size_t)M * N);
     F5B_CHECK_CUDA(cudaMemsetAsync(A, 0x3c, (size_t)M * ld * 2, st));
-    F5B_CHECK_CUDA(cudaMemsetAsync(W, 0x3c, (size_t)N * ld * 2, st));
+    F5B_CHECK_CUDA(cudaMemsetAsync(W, 0x3c, wbytes * ncopy, st));
     EpiParams ep;
     ep.out = O;
     ep.out_type = 1;
     ep.ldo = N;
     ep.n_valid = N;
-    timed([&] { tc_gemm(st, ctx.sm_count, A, ld, M, 1, W, ld, N, K, ep, nullptr, 0); });
+    if (which == 4 || which == 5 || which == 6) {  // 5 / 6: residual epilogue, 256-wide tiles, split-K 2 / 128-wide, split-K 2
+      float* R = arena.alloc_n<float>((size_t)M * N);
+      F5B_CHECK_CUDA(cudaMemsetAsync(R, 0, (size_t)M * N * 4, st));
+      ep.kind = EPI_RESID;
+      ep.resid = R;
+      ep.ldr = N;
+    }
+    const int fbn = which >= 64 ? which : which == 5 ? 256 : which == 6 ? 128 : 0;
+    const int fsp = which == 5 || which == 6 ? 2 : 0;
+    int turn = 0;
+    timed([&] {
+      tc_gemm(st, ctx.sm_count, A, ld, M, 1, W + (size_t)(turn % ncopy) * N * ld, ld, N, K, ep, nullptr, fbn, fsp);
+      ++turn;
+    });
   } else if (which == 1) {
     const int rows = M, heads = N, batches = K, inner = heads * 64;
     bf16* Q = arena.alloc_n<bf16>((size_t)batches * rows * 3 * inner);
@@ -320,6 +365,7 @@ int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, f
   }
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
+  cudaStreamDestroy(cs);
   F5B_API_END
 }
 

@@ -26,10 +26,70 @@ static constexpr int BM = 128;
 static constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
 static constexpr int A_STAGE_BYTES = BM * BK * 2;
 
+// ---------------------------------------------------------------------------------------------
+// epilogue: TMEM -> registers (bias / RoPE / activation / gate) -> 128B-swizzled smem staging -> TMA store, or TMA
+// reduce-add (fp32, performed in L2) for the gate * y + residual update.  No per-thread global stores: every global
+// write is a full-line bulk transfer, and the residual is never read back by the SM.
+// ---------------------------------------------------------------------------------------------
+static constexpr int EPI_NBUF = 3;
+static constexpr int EPI_BUF_BYTES = BM * 128;  // 128 rows x 128 B (32 fp32 or 64 16-bit columns)
+
+// bias_s / gate_s: this tile's bias and gate columns staged in shared memory (loaded while the MMAs run);
+// v[0..32) are accumulator columns [n, n+32) of one row, cs = offset of the chunk inside the tile.
+template <int ACT>
+__device__ __forceinline__ void epi_transform(const EpiParams& p, float* v, int n, int cs, int b, int pos, bool dead,
+                                              const float* bias_s, const float* gate_s) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const float4 bv = *reinterpret_cast<const float4*>(bias_s + cs + j);
+    v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
+  }
+  if (p.rope_cs != nullptr && n < p.rope_cols) {
+    const int within = n % p.rope_period;
+    if ((within >> 6) < p.rope_heads) {
+      const float4* cs4 = reinterpret_cast<const float4*>(p.rope_cs + (long long)pos * 64 + (within & 63));
+      float4 t[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] = __ldg(cs4 + j);  // (cos, sin) of two consecutive pairs; L1-resident per tile
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 tt = t[j >> 2];
+        float a = v[j], c = v[j + 1], e = v[j + 2], f = v[j + 3];
+        v[j] = a * tt.x - c * tt.y;
+        v[j + 1] = c * tt.x + a * tt.y;
+        v[j + 2] = e * tt.z - f * tt.w;
+        v[j + 3] = f * tt.z + e * tt.w;
+      }
+    }
+  }
+  if (ACT != ACT_NONE) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = act_apply(ACT, v[j]);
+  }
+  if (p.gate != nullptr) {
+    if (p.gate_bmod <= 1) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 gv = *reinterpret_cast<const float4*>(gate_s + cs + j);
+        v[j] *= gv.x; v[j + 1] *= gv.y; v[j + 2] *= gv.z; v[j + 3] *= gv.w;
+      }
+    } else {  // per-batch-element gates (f5b_forward with different times per utterance): row dependent, read directly
+      const float* g = p.gate + (long long)(b % p.gate_bmod) * p.gate_bstride + n;
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (n + j < p.n_valid) v[j] *= __ldg(g + j);
+    }
+  }
+  if (dead) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = 0.0f;
+  }
+}
+
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(192, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const TcGemmShape s, const EpiParams ep) {
+               const __grid_constant__ CUtensorMap tmO, const TcGemmShape s, const EpiParams ep) {
   constexpr int B_STAGE_BYTES = BN * BK * 2;
   constexpr uint32_t STAGE_TX = A_STAGE_BYTES + B_STAGE_BYTES;
   constexpr uint32_t ACC_COLS = 2 * BN;
@@ -38,7 +98,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_STAGE_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES));
+  uint8_t* sO = smem + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
+  float* sBias = reinterpret_cast<float*>(sO + EPI_NBUF * EPI_BUF_BYTES);  // [BN] bias, [BN] gate of the current tile
+  float* sGate = sBias + BN;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sGate + BN);
   uint64_t* empty = full + STAGES;
   uint64_t* tfull = empty + STAGES;
   uint64_t* tempty = tfull + 2;
@@ -47,11 +110,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int tiles_m = s.tiles_m_per_batch * s.batches;
-  const int total_tiles = tiles_m * s.tiles_n;
+  const int total_tiles = tiles_m * s.tiles_n * s.splits;  // work units: (tile, k-split)
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
+    prefetch_tmap(&tmO);
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
@@ -71,12 +135,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     // ------------------------------- TMA producer -------------------------------
     uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x) {
+      const int ks = unit % s.splits, tile = unit / s.splits;
       const int tm = tile / s.tiles_n, tn = tile - tm * s.tiles_n;
       const int bz = tm / s.tiles_m_per_batch;
       const int r0 = (tm - bz * s.tiles_m_per_batch) * BM;
       const int n0 = tn * BN;
-      for (int kb = 0; kb < s.num_kb; ++kb, ++it) {
+      const int kb0 = ks * s.num_kb / s.splits, kb1 = (ks + 1) * s.num_kb / s.splits;
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
         const uint32_t st = it % STAGES, ph = (it / STAGES) & 1u;
         mbar_wait(&empty[st], ph ^ 1u);
         mbar_expect_tx(&full[st], STAGE_TX);
@@ -93,12 +159,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp == 1 && lane == 0) {
     // ------------------------------- MMA issuer ---------------------------------
     uint32_t it = 0, tcount = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+    for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x, ++tcount) {
+      const int ks = unit % s.splits;
+      const int kb0 = ks * s.num_kb / s.splits, kb1 = (ks + 1) * s.num_kb / s.splits;
       const uint32_t acc = tcount & 1u, aph = (tcount >> 1) & 1u;
       mbar_wait(&tempty[acc], aph ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * BN;
-      for (int kb = 0; kb < s.num_kb; ++kb, ++it) {
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
         const uint32_t st = it % STAGES, ph = (it / STAGES) & 1u;
         mbar_wait(&full[st], ph);
         tc_fence_after();
@@ -108,7 +176,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int k = 0; k < BK / 16; ++k) {
           const uint64_t ad = umma_desc_sw128(a_addr + k * 32, 16, 1024);
           const uint64_t bd = umma_desc_sw128(b_addr + k * 32, 16, 1024);
-          umma_ss(d_tmem, ad, bd, s.idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_ss(d_tmem, ad, bd, s.idesc, (kb != kb0 || k != 0) ? 1u : 0u);
         }
         umma_commit(&empty[st]);  // frees the smem slot once these MMAs have read it
       }
@@ -117,30 +185,104 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else if (warp >= 2) {
     // ------------------------------- epilogue -----------------------------------
     const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are this warp's
-    uint32_t tcount = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+    const int rl = quarter * 32 + lane;  // row inside the tile
+    const bool issuer = threadIdx.x == 64;
+    const bool out32 = ep.kind == EPI_RESID || ep.out_type == OUT_F32;
+    uint32_t tcount = 0, nstore = 0;
+    for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x, ++tcount) {
+      const int ks = unit % s.splits, tile = unit / s.splits;
       const int tm = tile / s.tiles_n, tn = tile - tm * s.tiles_n;
       const int bz = tm / s.tiles_m_per_batch;
       const int r0 = (tm - bz * s.tiles_m_per_batch) * BM;
       const int n0 = tn * BN;
       const uint32_t acc = tcount & 1u, aph = (tcount >> 1) & 1u;
-      mbar_wait(&tfull[acc], aph);
-      tc_fence_after();
-      const int r = r0 + quarter * 32 + lane;
+      const bool with_bias = ks == 0;  // the bias joins exactly one of the partial sums
+      const int r = r0 + rl;
       const bool row_ok = r < s.rows_per_batch;
       const long long m = (long long)bz * s.rows_per_batch + r;
+      int b = 0, pos = 0;
+      bool dead = !row_ok;
+      if (row_ok) {
+        b = (int)(m / ep.rows_per_batch);
+        pos = (int)(m - (long long)b * ep.rows_per_batch);
+        if (ep.row_len != nullptr && pos >= ep.row_len[b]) dead = true;
+      }
+      // stage this tile's bias / gate columns while its MMAs are still running
+      for (int i = rl; i < BN; i += 128) {
+        const int n = n0 + i;
+        const bool in = n < ep.n_valid;
+        sBias[i] = (ep.bias != nullptr && with_bias && in) ? __ldg(ep.bias + n) : 0.0f;
+        sGate[i] = (ep.gate != nullptr && ep.gate_bmod <= 1 && in) ? __ldg(ep.gate + n) : 1.0f;
+      }
+      named_bar_sync(1, 128);
+      mbar_wait(&tfull[acc], aph);
+      tc_fence_after();
       const uint32_t t_row = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll 1
       for (int c = 0; c < BN; c += 32) {
+        const int n = n0 + c;
+        if (n >= s.N) break;  // uniform: the rest of the tile lies beyond the last column
         float v[32];
         tmem_ld_32x32(t_row + c, v);
         tmem_ld_wait();
-        if (row_ok && n0 + c < s.N) epi_apply<32>(ep, m, n0 + c, v);
+        switch (ep.act) {
+          case ACT_GELU_TANH: epi_transform<ACT_GELU_TANH>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
+          case ACT_GELU_ERF: epi_transform<ACT_GELU_ERF>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
+          case ACT_MISH: epi_transform<ACT_MISH>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
+          case ACT_SILU: epi_transform<ACT_SILU>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
+          default: epi_transform<ACT_NONE>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
+        }
+        uint8_t* buf = sO + (nstore % EPI_NBUF) * EPI_BUF_BYTES;
+        uint8_t* row = buf + rl * 128;
+        const int sw = rl & 7;
+        bool flush;
+        int c_first;
+        if (out32) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(row + ((j ^ sw) << 4)) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          flush = true;
+          c_first = n;
+        } else {
+          const int half = (c >> 5) & 1;
+          const bool f16 = ep.out_type == OUT_F16;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 pk;
+            if (f16) {
+              pk.x = pack_f16x2(v[8 * j], v[8 * j + 1]);
+              pk.y = pack_f16x2(v[8 * j + 2], v[8 * j + 3]);
+              pk.z = pack_f16x2(v[8 * j + 4], v[8 * j + 5]);
+              pk.w = pack_f16x2(v[8 * j + 6], v[8 * j + 7]);
+            } else {
+              pk.x = pack_bf16x2(v[8 * j], v[8 * j + 1]);
+              pk.y = pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+              pk.z = pack_bf16x2(v[8 * j + 4], v[8 * j + 5]);
+              pk.w = pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+            }
+            *reinterpret_cast<uint4*>(row + (((half * 4 + j) ^ sw) << 4)) = pk;
+          }
+          flush = half == 1 || c + 32 >= BN || n + 32 >= s.N;
+          c_first = n - half * 32;
+        }
+        if (flush) {
+          fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
+          named_bar_sync(1, 128);
+          if (issuer) {
+            if (ep.kind == EPI_RESID) tma_reduce_add_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
+            else tma_store_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
+            bulk_commit();
+            bulk_wait_read<1>();  // the buffer written two stores from now is free again
+          }
+          ++nstore;
+        }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
     }
+    if (issuer) bulk_wait<0>();
   }
 
   tc_fence_before();
@@ -168,6 +310,11 @@ static void load_encode() {
 
 void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box, int fp16) {
+  make_tmap(out, base, rank, dims, strides_bytes, box, fp16 ? OUT_F16 : OUT_BF16);
+}
+
+void make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+               const uint32_t* box, int elem_type) {
   load_encode();
   F5B_REQUIRE(g_encode != nullptr, "cuTensorMapEncodeTiled unavailable (no CUDA driver)");
   F5B_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
@@ -183,7 +330,10 @@ void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t
     gs[i] = strides_bytes[i];
     F5B_REQUIRE(gs[i] % 16 == 0, "TMA strides must be multiples of 16 bytes");
   }
-  CUresult r = g_encode(out, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx,
+  const CUtensorMapDataType dt = elem_type == OUT_F32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                 : elem_type == OUT_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                        : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUresult r = g_encode(out, dt, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx,
                         es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -193,46 +343,60 @@ void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t
 }
 
 template <int BN, int STAGES>
-static void launch_cfg(cudaStream_t st, int grid, const CUtensorMap& ta, const CUtensorMap& tb, const TcGemmShape& s,
-                       const EpiParams& ep) {
-  constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + 1024 + 256;
-  tc_gemm_kernel<BN, STAGES><<<grid, 192, smem, st>>>(ta, tb, s, ep);
+static constexpr int smem_bytes() {
+  return STAGES * (A_STAGE_BYTES + BN * BK * 2) + EPI_NBUF * EPI_BUF_BYTES + 2 * BN * 4 + 1024 + 256;
+}
+template <int BN, int STAGES>
+static void launch_cfg(cudaStream_t st, int grid, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
+                       const TcGemmShape& s, const EpiParams& ep) {
+  tc_gemm_kernel<BN, STAGES><<<grid, 192, smem_bytes<BN, STAGES>(), st>>>(ta, tb, to, s, ep);
   F5B_POST_LAUNCH();
 }
 
 template <int BN, int STAGES>
 static void config_one() {
-  constexpr int smem = STAGES * (A_STAGE_BYTES + BN * BK * 2) + 1024 + 256;
-  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  static_assert(smem_bytes<BN, STAGES>() <= 232448, "shared memory budget");
+  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      smem_bytes<BN, STAGES>()));
 }
 void tc_gemm_init_kernels() {
-  config_one<64, 8>();
-  config_one<128, 6>();
-  config_one<256, 4>();
+  config_one<64, 7>();
+  config_one<128, 5>();
+  config_one<256, 3>();
 }
 
-static int pick_bn(long long tiles_m, int N, int K, int sms, int force) {
-  if (force == 64 || force == 128 || force == 256) return force;
-  int best = 128;
-  double best_cost = 1e30;
+// Tile width and split-K factor.  Cost model from the measured sweep (tools/gemm_sweep.py, B200): one 64-deep k-block
+// costs ~0.26 / 0.30 / 0.37 us for 64 / 128 / 256-wide tiles (L2 operand traffic, not MMA issue, is the limit), a work
+// unit has ~1.5 us of fill + epilogue, and a CTA runs its units back to back.
+static void pick_tiling(long long tiles_m, int N, int K, int sms, bool can_split, int force_bn, int force_splits,
+                        int* bn_out, int* splits_out) {
   const int cand[3] = {64, 128, 256};
+  const double kb_us[3] = {0.26, 0.30, 0.37};
+  const int num_kb = (K + BK - 1) / BK;
+  double best_cost = 1e30;
+  *bn_out = 128;
+  *splits_out = 1;
   for (int i = 0; i < 3; ++i) {
-    int bn = cand[i];
-    long long tiles = tiles_m * ((N + bn - 1) / bn);
-    long long waves = (tiles + sms - 1) / sms;
-    double per_k16 = bn / 2.0 > 32.0 + bn / 4.0 ? bn / 2.0 : 32.0 + bn / 4.0;  // MMA issue vs smem operand reads
-    double tile_cost = per_k16 * (K / 16.0) + 1200.0 * bn / 128.0 / (waves > 1 ? 4.0 : 1.0);
-    double cost = waves * tile_cost;
-    if (cost < best_cost) {
-      best_cost = cost;
-      best = bn;
+    if (force_bn && cand[i] != force_bn) continue;
+    for (int sp = 1; sp <= 4; sp *= 2) {
+      if (force_splits && sp != force_splits) continue;
+      if (sp > 1 && (!can_split || num_kb / sp < 4)) continue;
+      long long units = tiles_m * ((N + cand[i] - 1) / cand[i]) * sp;
+      long long rounds = (units + sms - 1) / sms;
+      double unit_us = kb_us[i] * ((num_kb + sp - 1) / sp) + 1.5 * cand[i] / 128.0;
+      double cost = rounds * unit_us;
+      if (cost < best_cost) {
+        best_cost = cost;
+        *bn_out = cand[i];
+        *splits_out = sp;
+      }
     }
   }
-  return best;
 }
 
 void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int rows_per_batch, int batches,
-             const bf16* W, long long ldw, int N, int K, const EpiParams& ep, const TcConv* conv, int force_bn) {
+             const bf16* W, long long ldw, int N, int K, const EpiParams& ep, const TcConv* conv, int force_bn,
+             int force_splits) {
   F5B_REQUIRE(rows_per_batch > 0 && batches > 0 && N > 0 && K > 0, "empty GEMM");
   TcGemmShape s{};
   s.rows_per_batch = rows_per_batch;
@@ -245,13 +409,16 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
     F5B_REQUIRE(conv->cg % BK == 0, "tensor-core conv needs channels-per-group % 64 == 0");
     F5B_REQUIRE(K == conv->taps * conv->cg, "conv K mismatch");
     bn = 64;
+    s.splits = 1;
     s.conv = 1;
     s.conv_kb_per_tap = conv->cg / BK;
     s.conv_pad = conv->pad;
     s.conv_cg = conv->cg;
     a_cols = conv->channels;
   } else {
-    bn = pick_bn((long long)s.tiles_m_per_batch * batches, N, K, sm_count, force_bn);
+    const bool can_split = ep.kind == EPI_RESID && ep.act == ACT_NONE;
+    pick_tiling((long long)s.tiles_m_per_batch * batches, N, K, sm_count, can_split, force_bn, force_splits, &bn,
+                &s.splits);
     a_cols = K;
   }
   s.tiles_n = (N + bn - 1) / bn;
@@ -272,14 +439,33 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
     uint32_t box[2] = {BK, (uint32_t)bn};
     make_tmap_bf16(&tb, W, 2, dims, strides, box, fp16);
   }
-  long long total = (long long)s.tiles_m_per_batch * batches * s.tiles_n;
+  // output map: 3-D like A so that tile rows beyond a batch element (and the rows dropped by row_skip, which land at
+  // coordinate -1) are clipped by the TMA engine; box = 128 rows x 128 bytes, 128B-swizzled like the staging buffer
+  CUtensorMap to;
+  {
+    F5B_REQUIRE(ep.addend == nullptr, "tensor-core epilogue has no addend (use the residual form)");
+    const bool resid = ep.kind == EPI_RESID;
+    const int et = resid ? OUT_F32 : ep.out_type;
+    const int es = et == OUT_F32 ? 4 : 2;
+    const void* base = resid ? (const void*)ep.resid : (const void*)ep.out;
+    const long long ld = resid ? ep.ldr : ep.ldo;
+    const int ncols = ep.n_valid > 0 && ep.n_valid < N ? ep.n_valid : N;
+    F5B_REQUIRE(base != nullptr && ld > 0, "GEMM output missing");
+    F5B_REQUIRE(ep.row_skip == 0 || ep.rows_per_batch == rows_per_batch, "row_skip needs per-batch tiling");
+    const int out_rows = rows_per_batch - ep.row_skip;
+    uint64_t dims[3] = {(uint64_t)ncols, (uint64_t)out_rows, (uint64_t)batches};
+    uint64_t strides[2] = {(uint64_t)ld * es, (uint64_t)ld * es * (uint64_t)out_rows};
+    uint32_t box[3] = {(uint32_t)(128 / es), BM, 1};
+    make_tmap(&to, base, 3, dims, strides, box, et);
+  }
+  long long total = (long long)s.tiles_m_per_batch * batches * s.tiles_n * s.splits;
   int grid = (int)(total < sm_count ? total : sm_count);
   if (bn == 64)
-    launch_cfg<64, 8>(st, grid, ta, tb, s, ep);
+    launch_cfg<64, 7>(st, grid, ta, tb, to, s, ep);
   else if (bn == 128)
-    launch_cfg<128, 6>(st, grid, ta, tb, s, ep);
+    launch_cfg<128, 5>(st, grid, ta, tb, to, s, ep);
   else
-    launch_cfg<256, 4>(st, grid, ta, tb, s, ep);
+    launch_cfg<256, 3>(st, grid, ta, tb, to, s, ep);
 }
 
 }  // namespace f5b

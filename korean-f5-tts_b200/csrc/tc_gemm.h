@@ -16,6 +16,7 @@ struct TcGemmShape {
   int conv_kb_per_tap;
   int conv_pad;
   int conv_cg;
+  int splits;      // split-K factor (residual epilogue only: partial sums meet in the L2 reduce-add)
   unsigned idesc;  // tcgen05 instruction descriptor (operand formats differ between the bf16 and fp16 variants)
 };
 
@@ -29,13 +30,16 @@ struct TcConv {
   int fp16;      // operands are IEEE fp16 instead of bf16 (same tensor-core rate, 3 more mantissa bits)
 };
 
+void make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+               const uint32_t* box, int elem_type /* OUT_F32 / OUT_BF16 / OUT_F16 */);
 void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box, int fp16 = 0);
 
 // bf16 tensor-core GEMM: out = epilogue(A[rows, K] * W[N, K]^T).  A rows are [batches][rows_per_batch] with a
 // common leading dimension lda (elements).
 void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int rows_per_batch, int batches,
-             const bf16* W, long long ldw, int N, int K, const EpiParams& ep, const TcConv* conv, int force_bn);
+             const bf16* W, long long ldw, int N, int K, const EpiParams& ep, const TcConv* conv, int force_bn,
+             int force_splits = 0);
 
 // fp32 CUDA-core GEMM with the same epilogue (the correctness mode; also used for the tiny per-sample tables).
 void simt_gemm(cudaStream_t st, const float* A, long long lda, long long M, const float* W, long long ldw, int N,

@@ -292,7 +292,7 @@ void f5b_plan::ensure_ws(int B, int N, int nt, int steps, bool want_traj) {
   bf.cap_rows = rows; bf.capB = B; bf.cap_nt = nt; bf.cap_steps = steps; bf.capN = N; bf.traj_cap = traj_need;
   bf.y = A.alloc_n<float>((size_t)B * N * mel);
   bf.cond = A.alloc_n<float>((size_t)B * N * mel);
-  bf.v_out = A.alloc_n<float>((size_t)2 * B * N * mel);
+  bf.v_out = A.alloc_n<float>((size_t)2 * B * R * mel);  // UNetT keeps the time-token row; consumers skip it
   bf.x = A.alloc_n<float>((size_t)rows * d);
   bf.hproj = A.alloc_n<float>((size_t)rows * d);
   bf.te = A.alloc_n<float>((size_t)2 * B * N * td);
@@ -347,7 +347,7 @@ void f5b_plan::text_embed(cudaStream_t st, int B, int N, int nt, int batches, in
     e1.act = ACT_GELU_ERF;
     e1.bias = tb.b1;
     e1.out = bf.th;
-    e1.out_type = sizeof(T) == 2;
+    e1.out_type = sizeof(T) == 2 ? OUT_F16 : OUT_F32;
     e1.ldo = 2 * td;
     e1.n_valid = 2 * td;
     run_gemm(ctx, st, bf.tnorm, td, M, tb.pw1, e1);
@@ -464,7 +464,7 @@ void f5b_plan::input_embed(cudaStream_t st, int batches, int N, const int* lens_
 }
 
 // ---------------------------------------------------------------------------------------------
-// one backbone evaluation: bf.a_in -> bf.v_out [batches*N, mel]
+// one backbone evaluation: bf.a_in -> bf.v_out [batches*R, mel]  (R = N, or N + 1 with UNetT's leading time token)
 // ---------------------------------------------------------------------------------------------
 template <typename T>
 void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int tbl_bmod, const int* lens2,
@@ -510,7 +510,7 @@ void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int
     EpiParams eq;
     eq.bias = L.bqkv;
     eq.out = bf.qkv;
-    eq.out_type = is16;
+    eq.out_type = is16 ? OUT_BF16 : OUT_F32;  // q, k, v feed the attention kernel, which contracts bf16
     eq.ldo = 3 * inner;
     eq.n_valid = 3 * inner;
     eq.rows_per_batch = R;
@@ -520,7 +520,7 @@ void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int
     eq.rope_cs = bf.rope_cs;
     run_gemm(ctx, st, bf.norm, d, M, L.qkv, eq);
     if (is16)
-      tc_attention(st, (const bf16*)bf.qkv, (bf16*)bf.attn_o, batches, R, a.heads, kv_len, 0.125f);
+      tc_attention(st, (const bf16*)bf.qkv, (bf16*)bf.attn_o, batches, R, a.heads, kv_len, 0.125f, 1);
     else
       simt_attention(st, (const float*)bf.qkv, (float*)bf.attn_o, batches, R, a.heads, kv_len, 0.125f);
     EpiParams eo;
@@ -546,7 +546,7 @@ void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int
     e1.act = ACT_GELU_TANH;
     e1.bias = L.bff1;
     e1.out = bf.ffh;
-    e1.out_type = is16;
+    e1.out_type = is16 ? OUT_F16 : OUT_F32;
     e1.ldo = ffd;
     e1.n_valid = ffd;
     run_gemm(ctx, st, bf.norm, d, M, L.ff1, e1);
@@ -577,7 +577,6 @@ void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int
   } else {
     if (is16) xrms_norm<bf16x3>(st, bf.x, (bf16x3*)bf.norm3, M, d, norm_out_g);
     else xrms_norm<T>(st, bf.x, (T*)bf.norm, M, d, norm_out_g);
-    ep.row_skip = 1;  // norm_out(x)[:, 1:, :]
   }
   if (is16) run_gemm(ctx, st, bf.norm3, 3 * d, M, proj_out, ep, 64);
   else run_gemm(ctx, st, bf.norm, d, M, proj_out, ep, 64);

@@ -12,6 +12,10 @@
 namespace f5b {
 
 typedef __nv_bfloat16 bf16;
+// 16-bit type of the linear-layer operands (activations and weights) in the tensor-core mode: IEEE fp16.
+// tcgen05 kind::f16 contracts fp16 and bf16 at the same rate; fp16's 3 extra mantissa bits are what keeps the mode
+// inside the 2e-2 mel tolerance at full depth; the attention kernel's q/k/v/P stay bf16.
+typedef __half act16;
 
 // ---------------------------------------------------------------------------------------------
 // error handling: every C-ABI entry returns 0 or a negative code and leaves a thread-local message
@@ -40,9 +44,12 @@ long long last_call();
     }                                                                                             \
   } while (0)
 
+bool sync_debug();  // F5B_SYNC_DEBUG=1: synchronise after every launch so a device fault names its kernel
+
 #define F5B_POST_LAUNCH()                                                                        \
   do {                                                                                            \
     F5B_CHECK_CUDA(cudaGetLastError());                                                           \
+    if (f5b::sync_debug()) F5B_CHECK_CUDA(cudaDeviceSynchronize());                               \
     f5b::count_launch(1);                                                                         \
   } while (0)
 
@@ -86,7 +93,32 @@ struct EpiParams {
   const float* rope_cs = nullptr; // [rows_per_batch, 64] interleaved (cos_j, sin_j), j < 32
 };
 
+bool pdl_enabled(int kernel_id = 0);  // programmatic dependent launch for the per-step kernel chain (F5B_NO_PDL=1 switches it off)
+
 #if defined(__CUDACC__)
+
+// Programmatic dependent launch.  Every kernel of the per-step chain calls pdl_trigger() first (its successor may
+// be scheduled as soon as all of this grid's CTAs are resident) and pdl_wait() before it touches anything an earlier
+// kernel of the chain writes (or writes anything an earlier kernel reads); what runs before pdl_wait() -- barrier
+// init, TMEM allocation, descriptor prefetch, loads of weights / per-call tables -- overlaps the predecessor's tail.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... P, typename... A>
+inline void launch_pdl_id(int kernel_id, void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                          A&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled(kernel_id) ? 1 : 0;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  F5B_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, P(args)...));
+}
 
 __device__ __forceinline__ float act_apply(int act, float x) {
   switch (act) {
@@ -131,6 +163,7 @@ __device__ __forceinline__ float warp_max(float v) {
 
 __device__ __forceinline__ float ld_as_float(const float* p) { return *p; }
 __device__ __forceinline__ float ld_as_float(const bf16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ float ld_as_float(const __half* p) { return __half2float(*p); }
 __device__ __forceinline__ void st_from_float(float* p, float v) { *p = v; }
 __device__ __forceinline__ void st_from_float(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
 __device__ __forceinline__ void st_from_float(__half* p, float v) { *p = __float2half_rn(v); }

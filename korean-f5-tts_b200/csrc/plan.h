@@ -36,7 +36,8 @@ class Arena {
 // A weight matrix usable by either contraction path: fp32 [N, K] always; bf16 [N, ldw] in bf16 mode.
 struct WMat {
   const float* f32 = nullptr;
-  const bf16* b16 = nullptr;
+  const bf16* b16 = nullptr;  // 16-bit copy: IEEE fp16 bits when `fp16`, bf16 otherwise
+  int fp16 = 0;
   int N = 0, K = 0;
   long long ld32 = 0, ld16 = 0;
 };
@@ -55,7 +56,7 @@ class WeightStore {
 // out = epilogue(A[M,K] W^T): dispatch on the plan's precision mode.  A is `float` (fp32 mode) or `bf16`.
 void run_gemm(const DeviceCtx& ctx, cudaStream_t st, const void* A, long long lda, long long M, const WMat& w,
               const EpiParams& ep, int force_bn = 0);
-WMat make_wmat(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K);
+WMat make_wmat(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K, int fp16 = 1);
 WMat make_wmat_split3(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K);
 // cat rows of several [Ni, K] fp32 matrices into one device matrix
 float* concat_rows(Arena* arena, cudaStream_t st, const std::vector<std::pair<const float*, long long>>& parts);

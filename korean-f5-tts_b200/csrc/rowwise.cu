@@ -33,6 +33,12 @@ __device__ __forceinline__ float4 load4<float>(const float* p) {
   return *reinterpret_cast<const float4*>(p);
 }
 template <>
+__device__ __forceinline__ float4 load4<__half>(const __half* p) {
+  uint2 r = *reinterpret_cast<const uint2*>(p);
+  float2 fa = __half22float2(*reinterpret_cast<__half2*>(&r.x)), fb = __half22float2(*reinterpret_cast<__half2*>(&r.y));
+  return make_float4(fa.x, fa.y, fb.x, fb.y);
+}
+template <>
 __device__ __forceinline__ float4 load4<bf16>(const bf16* p) {
   uint2 r = *reinterpret_cast<const uint2*>(p);
   __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&r.x);
@@ -111,11 +117,26 @@ __global__ void __launch_bounds__(256)
 ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d, const float* __restrict__ mul,
                   const float* __restrict__ add, float mul_off, long long vec_bstride, int rows_per_batch, int bmod,
                   float eps) {
+  pdl_trigger();
   const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (m >= M) return;
   const float* xr = x + m * d;
-  float4 buf[8];
+  const int b = (int)((m / rows_per_batch) % bmod);
+  const float* mu = mul ? mul + b * vec_bstride : nullptr;
+  const float* ad = add ? add + b * vec_bstride : nullptr;
+  float4 buf[8], g[8], h[8];
+  // the modulation vectors are per-call tables (not written inside the step chain): fetched before the dependency wait
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < d) {
+      g[i] = mu ? __ldg(reinterpret_cast<const float4*>(mu + c))
+                : make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
+      h[i] = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
+    }
+  }
+  pdl_wait();
   float s = 0.0f;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
@@ -131,25 +152,21 @@ ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M,
   for (int i = 0; i < 8; ++i) {
     const int c = i * 128 + lane * 4;
     if (c < d) {
-      float a = buf[i].x - mean, b = buf[i].y - mean, cc = buf[i].z - mean, dd = buf[i].w - mean;
-      q += (a * a + b * b) + (cc * cc + dd * dd);
+      float a = buf[i].x - mean, bb = buf[i].y - mean, cc = buf[i].z - mean, dd = buf[i].w - mean;
+      q += (a * a + bb * bb) + (cc * cc + dd * dd);
     }
   }
   const float rstd = rsqrtf(warp_sum(q) / d + eps);
-  const int b = (int)((m / rows_per_batch) % bmod);
-  const float* mu = mul ? mul + b * vec_bstride : nullptr;
-  const float* ad = add ? add + b * vec_bstride : nullptr;
   T* orow = out + m * d * RowOut<T>::kWidth;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int c = i * 128 + lane * 4;
     if (c < d) {
       const float4 v = buf[i];
-      float4 g = mu ? __ldg(reinterpret_cast<const float4*>(mu + c)) : make_float4(0, 0, 0, 0);
-      float4 h = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
-      if (!mu) g = make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
-      RowOut<T>::st(orow, c, d, (v.x - mean) * rstd * (mul_off + g.x) + h.x, (v.y - mean) * rstd * (mul_off + g.y) + h.y,
-                    (v.z - mean) * rstd * (mul_off + g.z) + h.z, (v.w - mean) * rstd * (mul_off + g.w) + h.w);
+      RowOut<T>::st(orow, c, d, (v.x - mean) * rstd * (mul_off + g[i].x) + h[i].x,
+                    (v.y - mean) * rstd * (mul_off + g[i].y) + h[i].y,
+                    (v.z - mean) * rstd * (mul_off + g[i].z) + h[i].z,
+                    (v.w - mean) * rstd * (mul_off + g[i].w) + h[i].w);
     }
   }
 }
@@ -159,8 +176,8 @@ void ln_mod(cudaStream_t st, const float* x, T* out, long long M, int d, const f
             float mul_off, long long vec_bstride, int rows_per_batch, int bmod, float eps) {
   F5B_REQUIRE(d % 4 == 0, "LayerNorm width must be a multiple of 4");
   if (d <= 1024)
-    ln_mod_reg_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride,
-                                                            rows_per_batch, bmod < 1 ? 1 : bmod, eps);
+    launch_pdl_id(4, ln_mod_reg_kernel<T>, dim3(ceil_div_ll(M, 8)), dim3(256), 0, st, x, out, M, d, mul, add, mul_off,
+               vec_bstride, rows_per_batch, bmod < 1 ? 1 : bmod, eps);
   else
     ln_mod_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride, rows_per_batch,
                                                         bmod < 1 ? 1 : bmod, eps);
@@ -169,6 +186,8 @@ void ln_mod(cudaStream_t st, const float* x, T* out, long long M, int d, const f
 template void ln_mod<float>(cudaStream_t, const float*, float*, long long, int, const float*, const float*, float,
                             long long, int, int, float);
 template void ln_mod<bf16>(cudaStream_t, const float*, bf16*, long long, int, const float*, const float*, float,
+                           long long, int, int, float);
+template void ln_mod<__half>(cudaStream_t, const float*, __half*, long long, int, const float*, const float*, float,
                            long long, int, int, float);
 template void ln_mod<bf16x3>(cudaStream_t, const float*, bf16x3*, long long, int, const float*, const float*, float,
                              long long, int, int, float);
@@ -206,6 +225,7 @@ void xrms_norm(cudaStream_t st, const float* x, T* out, long long M, int d, cons
 }
 template void xrms_norm<float>(cudaStream_t, const float*, float*, long long, int, const float*);
 template void xrms_norm<bf16>(cudaStream_t, const float*, bf16*, long long, int, const float*);
+template void xrms_norm<__half>(cudaStream_t, const float*, __half*, long long, int, const float*);
 template void xrms_norm<bf16x3>(cudaStream_t, const float*, bf16x3*, long long, int, const float*);
 
 // ---------------------------------------------------------------------------------------------
@@ -281,6 +301,8 @@ template void dwconv7_ln<float>(cudaStream_t, const float*, float*, int, int, in
                                 const float*, const float*, const float*, float);
 template void dwconv7_ln<bf16>(cudaStream_t, const float*, bf16*, int, int, int, const int*, const float*,
                                const float*, const float*, const float*, float);
+template void dwconv7_ln<__half>(cudaStream_t, const float*, __half*, int, int, int, const int*, const float*,
+                               const float*, const float*, const float*, float);
 
 // ---------------------------------------------------------------------------------------------
 // GRN: gx[b,c] = ||h[b,:len,c]||_2 ; nx = gx / (mean_c gx + 1e-6) ; h = gamma*(h*nx) + beta + h
@@ -352,6 +374,7 @@ void grn_inplace(cudaStream_t st, T* h, int batches, int rows, int C, const int*
 }
 template void grn_inplace<float>(cudaStream_t, float*, int, int, int, const int*, const float*, const float*, float*);
 template void grn_inplace<bf16>(cudaStream_t, bf16*, int, int, int, const int*, const float*, const float*, float*);
+template void grn_inplace<__half>(cudaStream_t, __half*, int, int, int, const int*, const float*, const float*, float*);
 
 // ---------------------------------------------------------------------------------------------
 // text token lookup (+ sinus position table, + padding mask); one warp per (batch, position)
@@ -437,18 +460,22 @@ void build_a_in(cudaStream_t st, float* a_in, long long ld, int B, int batches, 
 
 // v [branches*B*rows, mel]: branch 0 = cond prediction, branch 1 = uncond.  dt == 0 with v == null just scatters y.
 __global__ void __launch_bounds__(256)
-cfg_euler_kernel(float* __restrict__ y, const float* __restrict__ v, float* __restrict__ a_in, long long ld, int B,
-                 int branches, int rows, int mel, float dt, float cfg, float* __restrict__ traj, long long total) {
+cfg_euler_kernel(float* __restrict__ y, const float* __restrict__ v, int v_lead, float* __restrict__ a_in, long long ld,
+                 int B, int branches, int rows, int mel, float dt, float cfg, float* __restrict__ traj, long long total) {
+  pdl_trigger();
+  pdl_wait();
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= total) return;
   const long long m = i / mel;
   const int c = (int)(i - m * mel);
   float yv = y[i];
   if (v != nullptr) {
-    float pc = v[i];
+    const long long bb = m / rows;  // batch element; v has rows + v_lead rows per element
+    const long long vi = i + (bb + 1) * (long long)v_lead * mel;
+    float pc = v[vi];
     float vel = pc;
     if (branches == 2) {
-      float pu = v[total + i];
+      float pu = v[vi + (long long)B * (rows + v_lead) * mel];
       vel = pc + (pc - pu) * cfg;
     }
     yv = yv + dt * vel;
@@ -458,11 +485,11 @@ cfg_euler_kernel(float* __restrict__ y, const float* __restrict__ v, float* __re
   st_from_float(a_in + m * ld + c, yv);
   if (branches == 2) st_from_float(a_in + (m + (long long)B * rows) * ld + c, yv);
 }
-void cfg_euler(cudaStream_t st, float* y, const float* v, float* a_in, long long ld, int B, int branches, int rows,
+void cfg_euler(cudaStream_t st, float* y, const float* v, int v_lead_rows, float* a_in, long long ld, int B, int branches, int rows,
                int mel, float dt, float cfg, float* traj_slot) {
   long long total = (long long)B * rows * mel;
-  cfg_euler_kernel<<<ceil_div_ll(total, 256), 256, 0, st>>>(y, v, a_in, ld, B, branches, rows, mel, dt, cfg,
-                                                               traj_slot, total);
+  launch_pdl_id(8, cfg_euler_kernel, dim3(ceil_div_ll(total, 256)), dim3(256), 0, st, y, v, v_lead_rows, a_in, ld, B, branches, rows, mel,
+             dt, cfg, traj_slot, total);
   F5B_POST_LAUNCH();
 }
 
@@ -470,6 +497,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 cast_mask_kernel(const float* __restrict__ x, T* __restrict__ out, int rows, int d4, const int* __restrict__ row_len,
                  long long total4, float* __restrict__ copy) {
+  pdl_trigger();
+  pdl_wait();
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= total4) return;
   const long long m = i / d4;
@@ -484,7 +513,8 @@ cast_mask_kernel(const float* __restrict__ x, T* __restrict__ out, int rows, int
 template <typename T>
 void cast_mask(cudaStream_t st, const float* x, T* out, int batches, int rows, int d, const int* row_len, float* copy) {
   long long total4 = (long long)batches * rows * d / 4;
-  cast_mask_kernel<T><<<ceil_div_ll(total4, 256), 256, 0, st>>>(x, out, rows, d / 4, row_len, total4, copy);
+  launch_pdl_id(16, cast_mask_kernel<T>, dim3(ceil_div_ll(total4, 256)), dim3(256), 0, st, x, out, rows, d / 4, row_len, total4,
+             copy);
   F5B_POST_LAUNCH();
 }
 template void cast_mask<float>(cudaStream_t, const float*, float*, int, int, int, const int*, float*);
@@ -571,5 +601,6 @@ void concat2(cudaStream_t st, const float* a, const float* b, T* out, long long 
 }
 template void concat2<float>(cudaStream_t, const float*, const float*, float*, long long, int);
 template void concat2<bf16>(cudaStream_t, const float*, const float*, bf16*, long long, int);
+template void concat2<__half>(cudaStream_t, const float*, const float*, __half*, long long, int);
 
 }  // namespace f5b

@@ -41,8 +41,9 @@ void mask_rows(cudaStream_t st, float* x, long long M, int d, const unsigned cha
 // A_in[m, 100:200) = cond (zero for the uncond branch), A_in[m, 200:200+td) = text embedding.
 void build_a_in(cudaStream_t st, float* a_in, long long ld, int B, int batches, int rows, int mel, int td,
                 const float* cond, const float* text_emb, int uncond_from);
+// v holds `v_lead_rows` extra leading rows per batch element (UNetT's time token) that are skipped.
 // y (+)= ...; also scatters y into the x columns of A_in for every branch and, optionally, into the trajectory.
-void cfg_euler(cudaStream_t st, float* y, const float* v, float* a_in, long long ld, int B, int branches, int rows,
+void cfg_euler(cudaStream_t st, float* y, const float* v, int v_lead_rows, float* a_in, long long ld, int B, int branches, int rows,
                int mel, float dt, float cfg, float* traj_slot);
 
 // out = masked cast of x; copy (optional) = x unchanged (seeds the residual stream for the conv pos-emb epilogue)

@@ -1,5 +1,6 @@
 // Runtime plumbing: errors, arena, weight store, contraction dispatch, kernel-level C entry points.
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 
 #include "plan.h"
@@ -9,6 +10,16 @@ namespace f5b {
 static thread_local std::string g_err;
 void set_error(const std::string& msg) { g_err = msg; }
 const char* get_error() { return g_err.c_str(); }
+
+bool pdl_enabled(int kernel_id) {  // F5B_PDL_MASK (debug): bit set = that kernel family launches with PDL
+  static const bool on = std::getenv("F5B_NO_PDL") == nullptr;
+  static const int mask = std::getenv("F5B_PDL_MASK") ? std::atoi(std::getenv("F5B_PDL_MASK")) : ~0;
+  return on && (kernel_id == 0 || (mask & kernel_id) != 0);
+}
+bool sync_debug() {
+  static const bool on = std::getenv("F5B_SYNC_DEBUG") != nullptr;
+  return on;
+}
 
 static std::atomic<long long> g_launches{0};
 void count_launch(long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
@@ -56,13 +67,14 @@ const float* WeightStore::get(const std::string& name, long long numel) const {
   return it->second.p;
 }
 
-__global__ void pad_convert_kernel(const float* __restrict__ in, bf16* __restrict__ out, int K, long long ld,
+template <typename T>
+__global__ void pad_convert_kernel(const float* __restrict__ in, T* __restrict__ out, int K, long long ld,
                                    long long total) {
   long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= total) return;
   long long r = i / ld;
   int c = (int)(i - r * ld);
-  out[i] = __float2bfloat16_rn(c < K ? in[r * K + c] : 0.0f);
+  st_from_float(out + i, c < K ? in[r * K + c] : 0.0f);
 }
 
 __global__ void widen_kernel(const bf16* __restrict__ in, float* __restrict__ o, long long n) {
@@ -70,7 +82,7 @@ __global__ void widen_kernel(const bf16* __restrict__ in, float* __restrict__ o,
   if (i < n) o[i] = __bfloat162float(in[i]);
 }
 
-WMat make_wmat(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K) {
+WMat make_wmat(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float* w32, int N, int K, int fp16) {
   WMat m;
   m.f32 = w32;
   m.N = N;
@@ -80,7 +92,12 @@ WMat make_wmat(const DeviceCtx& ctx, Arena* arena, cudaStream_t st, const float*
     long long ld = (K + 7) / 8 * 8;
     bf16* p = arena->alloc_n<bf16>((size_t)N * ld);
     long long total = (long long)N * ld;
-    pad_convert_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(w32, p, K, ld, total);
+    if (fp16)
+      pad_convert_kernel<__half><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(w32, reinterpret_cast<__half*>(p), K,
+                                                                                 ld, total);
+    else
+      pad_convert_kernel<bf16><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(w32, p, K, ld, total);
+    m.fp16 = fp16;
     F5B_POST_LAUNCH();
     m.b16 = p;
     m.ld16 = ld;
@@ -146,7 +163,7 @@ void run_gemm(const DeviceCtx& ctx, cudaStream_t st, const void* A, long long ld
       nb = (int)(M / ep.rows_per_batch);
     }
     tc_gemm(st, ctx.sm_count, reinterpret_cast<const bf16*>(A), lda, rpb, nb, w.b16, w.ld16, w.N, w.K, ep, nullptr,
-            force_bn);
+            force_bn, 0, w.fp16);
   } else {
     simt_gemm(st, reinterpret_cast<const float*>(A), lda, M, w.f32, w.ld32, w.N, w.K, ep);
   }
@@ -232,10 +249,12 @@ int f5b_device_check(int device) {
 int f5b_op_gemm(int32_t mode, const float* A, const float* W, const float* bias, int32_t M, int32_t N, int32_t K,
                 int32_t act, float* out, int32_t force_bn, int32_t device, void* stream) {
   F5B_API_BEGIN
+  const int fp16 = mode == 2;  // kernel-level switch: 1 = bf16 operands, 2 = IEEE fp16 operands
+  if (mode == 2) mode = F5B_MODE_BF16;
   DeviceCtx ctx = open_device(device, mode);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   Arena arena;
-  WMat w = make_wmat(ctx, &arena, st, W, N, K);
+  WMat w = make_wmat(ctx, &arena, st, W, N, K, fp16);
   EpiParams ep;
   ep.act = act;
   ep.bias = bias;
@@ -243,7 +262,7 @@ int f5b_op_gemm(int32_t mode, const float* A, const float* W, const float* bias,
   ep.ldo = N;
   ep.n_valid = N;
   if (mode == F5B_MODE_BF16) {
-    WMat tmp = make_wmat(ctx, &arena, st, A, M, K);  // pad K to a multiple of 8 and convert, like a weight
+    WMat tmp = make_wmat(ctx, &arena, st, A, M, K, fp16);  // pad K to a multiple of 8 and convert, like a weight
     run_gemm(ctx, st, tmp.b16, tmp.ld16, M, w, ep, force_bn);
   } else {
     run_gemm(ctx, st, A, K, M, w, ep, 0);

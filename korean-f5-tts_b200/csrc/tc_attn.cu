@@ -39,7 +39,7 @@ __device__ __forceinline__ float fast_exp2(float x) {
 
 __global__ void __launch_bounds__(320, 1)
 tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, int rows, int heads,
-               const int* __restrict__ kv_len, float scale_log2) {
+               const int* __restrict__ kv_len, float scale_log2, int out_f16) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem;                                  // 2 tiles
@@ -55,6 +55,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
   uint64_t* o_done = p_full + 2;                  // [2]  MMA -> softmax: the last PV_t has completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
 
+  pdl_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 2 * AT_BQ, h = blockIdx.y, b = blockIdx.z;
   const int inner = heads * AT_D;
@@ -80,6 +81,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // qkv comes from the previous kernel; everything above overlapped its tail
 
   if (warp == 8) {
     if (lane == 0) {
@@ -232,10 +234,17 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
 #pragma unroll
         for (int d = 0; d < 32; d += 8) {
           uint4 pk;
-          pk.x = pack_bf16x2(o[d] * inv, o[d + 1] * inv);
-          pk.y = pack_bf16x2(o[d + 2] * inv, o[d + 3] * inv);
-          pk.z = pack_bf16x2(o[d + 4] * inv, o[d + 5] * inv);
-          pk.w = pack_bf16x2(o[d + 6] * inv, o[d + 7] * inv);
+          if (out_f16) {
+            pk.x = pack_f16x2(o[d] * inv, o[d + 1] * inv);
+            pk.y = pack_f16x2(o[d + 2] * inv, o[d + 3] * inv);
+            pk.z = pack_f16x2(o[d + 4] * inv, o[d + 5] * inv);
+            pk.w = pack_f16x2(o[d + 6] * inv, o[d + 7] * inv);
+          } else {
+            pk.x = pack_bf16x2(o[d] * inv, o[d + 1] * inv);
+            pk.y = pack_bf16x2(o[d + 2] * inv, o[d + 3] * inv);
+            pk.z = pack_bf16x2(o[d + 4] * inv, o[d + 5] * inv);
+            pk.w = pack_bf16x2(o[d + 6] * inv, o[d + 7] * inv);
+          }
           *reinterpret_cast<uint4*>(op + c + d) = pk;
         }
       }
@@ -251,7 +260,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
 }
 
 void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int rows, int heads, const int* kv_len,
-                  float scale) {
+                  float scale, int out_f16) {
   const int inner = heads * AT_D;
   CUtensorMap tm;
   uint64_t dims[3] = {(uint64_t)3 * inner, (uint64_t)rows, (uint64_t)batches};
@@ -259,7 +268,8 @@ void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int 
   uint32_t box[3] = {AT_D, 128, 1};
   make_tmap_bf16(&tm, qkv, 3, dims, strides, box);
   dim3 grid((rows + 2 * AT_BQ - 1) / (2 * AT_BQ), heads, batches);
-  tc_attn_kernel<<<grid, 320, AT_SMEM, st>>>(tm, out, rows, heads, kv_len, scale * 1.4426950408889634f);
+  launch_pdl_id(2, tc_attn_kernel, grid, dim3(320), AT_SMEM, st, tm, out, rows, heads, kv_len,
+             scale * 1.4426950408889634f, out_f16);
   F5B_POST_LAUNCH();
 }
 

@@ -16,6 +16,7 @@
 #include "tc_gemm.h"
 
 #include <cudaTypedefs.h>
+#include <cstdlib>
 #include <mutex>
 
 namespace f5b {
@@ -34,37 +35,66 @@ static constexpr int A_STAGE_BYTES = BM * BK * 2;
 static constexpr int EPI_NBUF = 3;
 static constexpr int EPI_BUF_BYTES = BM * 128;  // 128 rows x 128 B (32 fp32 or 64 16-bit columns)
 
+// Activations of the tensor-core epilogue: single-MUFU forms (tanh.approx, ex2.approx, rcp.approx).  Their error
+// (~2^-11 relative) is below the rounding of the 16-bit value that is stored; the fp32 mode keeps libm (common.cuh).
+__device__ __forceinline__ float fast_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+template <int ACT>
+__device__ __forceinline__ float act_fast(float x) {
+  if (ACT == ACT_GELU_TANH) {
+    const float u = 0.7978845608028654f * (x + 0.044715f * x * x * x);
+    return 0.5f * x * (1.0f + fast_tanh(u));
+  } else if (ACT == ACT_MISH) {
+    // x * tanh(softplus(x)) = x * (n^2 - 1) / (n^2 + 1), n = 1 + e^x
+    const float e = __expf(fminf(x, 20.0f));
+    const float n2 = (1.0f + e) * (1.0f + e);
+    return x * __fdividef(n2 - 1.0f, n2 + 1.0f);
+  } else if (ACT == ACT_SILU) {
+    return __fdividef(x, 1.0f + __expf(-x));
+  } else if (ACT == ACT_GELU_ERF) {
+    return act_apply(ACT_GELU_ERF, x);  // exact erf: ConvNeXt / Vocos blocks, off the per-step path
+  }
+  return x;
+}
+
 // bias_s / gate_s: this tile's bias and gate columns staged in shared memory (loaded while the MMAs run);
 // v[0..32) are accumulator columns [n, n+32) of one row, cs = offset of the chunk inside the tile.
+template <int HALF>
+__device__ __forceinline__ void rope_rotate(float* v, const float4 (&t)[16]) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 4) {
+    const float4 tt = t[HALF * 8 + (j >> 2)];  // (cos, sin) of two consecutive interleaved pairs
+    float a = v[j], c = v[j + 1], e = v[j + 2], f = v[j + 3];
+    v[j] = a * tt.x - c * tt.y;
+    v[j + 1] = c * tt.x + a * tt.y;
+    v[j + 2] = e * tt.z - f * tt.w;
+    v[j + 3] = f * tt.z + e * tt.w;
+  }
+}
+
 template <int ACT>
 __device__ __forceinline__ void epi_transform(const EpiParams& p, float* v, int n, int cs, int b, int pos, bool dead,
-                                              const float* bias_s, const float* gate_s) {
+                                              const float* bias_s, const float* gate_s, const float4 (&rope)[16],
+                                              bool has_rope) {
 #pragma unroll
   for (int j = 0; j < 32; j += 4) {
     const float4 bv = *reinterpret_cast<const float4*>(bias_s + cs + j);
     v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
   }
-  if (p.rope_cs != nullptr && n < p.rope_cols) {
+  if (has_rope && n < p.rope_cols) {
     const int within = n % p.rope_period;
     if ((within >> 6) < p.rope_heads) {
-      const float4* cs4 = reinterpret_cast<const float4*>(p.rope_cs + (long long)pos * 64 + (within & 63));
-      float4 t[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) t[j] = __ldg(cs4 + j);  // (cos, sin) of two consecutive pairs; L1-resident per tile
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        const float4 tt = t[j >> 2];
-        float a = v[j], c = v[j + 1], e = v[j + 2], f = v[j + 3];
-        v[j] = a * tt.x - c * tt.y;
-        v[j + 1] = c * tt.x + a * tt.y;
-        v[j + 2] = e * tt.z - f * tt.w;
-        v[j + 3] = f * tt.z + e * tt.w;
-      }
+      // rope[0..16): this row's 32 (cos, sin) pairs, loaded once per tile; a 32-column chunk is half a head
+      if (within & 32) rope_rotate<1>(v, rope);
+      else rope_rotate<0>(v, rope);
     }
   }
   if (ACT != ACT_NONE) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = act_apply(ACT, v[j]);
+    for (int j = 0; j < 32; ++j) v[j] = act_fast<ACT>(v[j]);
   }
   if (p.gate != nullptr) {
     if (p.gate_bmod <= 1) {
@@ -107,6 +137,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
+  pdl_trigger();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int tiles_m = s.tiles_m_per_batch * s.batches;
@@ -134,7 +165,21 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (warp == 0 && lane == 0) {
     // ------------------------------- TMA producer -------------------------------
+    // The weights do not depend on the previous kernel: the W tiles of the first ring fill are requested BEFORE the
+    // programmatic-dependency wait, so their HBM latency overlaps the predecessor's tail; the A tiles follow after it.
     uint32_t it = 0;
+    int pre = 0;
+    if (blockIdx.x < total_tiles) {
+      const int ks = blockIdx.x % s.splits, tile = blockIdx.x / s.splits;
+      const int tn = tile % s.tiles_n;
+      const int kb0 = ks * s.num_kb / s.splits, kb1 = (ks + 1) * s.num_kb / s.splits;
+      pre = kb1 - kb0 < STAGES ? kb1 - kb0 : STAGES;
+      for (int i = 0; i < pre; ++i) {
+        mbar_expect_tx(&full[i], STAGE_TX);
+        tma_load_2d(sB + i * B_STAGE_BYTES, &tmB, &full[i], (kb0 + i) * BK, tn * BN);
+      }
+    }
+    pdl_wait();
     for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x) {
       const int ks = unit % s.splits, tile = unit / s.splits;
       const int tm = tile / s.tiles_n, tn = tile - tm * s.tiles_n;
@@ -144,8 +189,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int kb0 = ks * s.num_kb / s.splits, kb1 = (ks + 1) * s.num_kb / s.splits;
       for (int kb = kb0; kb < kb1; ++kb, ++it) {
         const uint32_t st = it % STAGES, ph = (it / STAGES) & 1u;
-        mbar_wait(&empty[st], ph ^ 1u);
-        mbar_expect_tx(&full[st], STAGE_TX);
+        const bool w_requested = (int)it < pre;  // first ring fill: W is already in flight, the slot is fresh
+        if (!w_requested) {
+          mbar_wait(&empty[st], ph ^ 1u);
+          mbar_expect_tx(&full[st], STAGE_TX);
+        }
         int a_c0 = kb * BK, a_c1 = r0;
         if (s.conv) {
           const int tap = kb / s.conv_kb_per_tap, sub = kb - tap * s.conv_kb_per_tap;
@@ -153,7 +201,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           a_c1 = r0 + tap - s.conv_pad;
         }
         tma_load_3d(sA + st * A_STAGE_BYTES, &tmA, &full[st], a_c0, a_c1, bz);
-        tma_load_2d(sB + st * B_STAGE_BYTES, &tmB, &full[st], kb * BK, n0);
+        if (!w_requested) tma_load_2d(sB + st * B_STAGE_BYTES, &tmB, &full[st], kb * BK, n0);
       }
     }
   } else if (warp == 1 && lane == 0) {
@@ -215,6 +263,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         sGate[i] = (ep.gate != nullptr && ep.gate_bmod <= 1 && in) ? __ldg(ep.gate + n) : 1.0f;
       }
       named_bar_sync(1, 128);
+      float4 rope_reg[16];
+      const bool has_rope = ep.rope_cs != nullptr && n0 < ep.rope_cols;  // uniform per tile
+      if (has_rope) {
+        const float4* src = reinterpret_cast<const float4*>(ep.rope_cs + (long long)pos * 64);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) rope_reg[i] = __ldg(src + i);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) rope_reg[i] = make_float4(1.0f, 0.0f, 1.0f, 0.0f);
+      }
       mbar_wait(&tfull[acc], aph);
       tc_fence_after();
       const uint32_t t_row = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -226,11 +284,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tmem_ld_32x32(t_row + c, v);
         tmem_ld_wait();
         switch (ep.act) {
-          case ACT_GELU_TANH: epi_transform<ACT_GELU_TANH>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
-          case ACT_GELU_ERF: epi_transform<ACT_GELU_ERF>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
-          case ACT_MISH: epi_transform<ACT_MISH>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
-          case ACT_SILU: epi_transform<ACT_SILU>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
-          default: epi_transform<ACT_NONE>(ep, v, n, c, b, pos, dead, sBias, sGate); break;
+          case ACT_GELU_TANH: epi_transform<ACT_GELU_TANH>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+          case ACT_GELU_ERF: epi_transform<ACT_GELU_ERF>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+          case ACT_MISH: epi_transform<ACT_MISH>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+          case ACT_SILU: epi_transform<ACT_SILU>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+          default: epi_transform<ACT_NONE>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
         }
         uint8_t* buf = sO + (nstore % EPI_NBUF) * EPI_BUF_BYTES;
         uint8_t* row = buf + rl * 128;
@@ -349,7 +407,7 @@ static constexpr int smem_bytes() {
 template <int BN, int STAGES>
 static void launch_cfg(cudaStream_t st, int grid, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
                        const TcGemmShape& s, const EpiParams& ep) {
-  tc_gemm_kernel<BN, STAGES><<<grid, 192, smem_bytes<BN, STAGES>(), st>>>(ta, tb, to, s, ep);
+  launch_pdl_id(1, tc_gemm_kernel<BN, STAGES>, dim3(grid), dim3(192), smem_bytes<BN, STAGES>(), st, ta, tb, to, s, ep);
   F5B_POST_LAUNCH();
 }
 
@@ -396,7 +454,7 @@ static void pick_tiling(long long tiles_m, int N, int K, int sms, bool can_split
 
 void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int rows_per_batch, int batches,
              const bf16* W, long long ldw, int N, int K, const EpiParams& ep, const TcConv* conv, int force_bn,
-             int force_splits) {
+             int force_splits, int fp16_operands) {
   F5B_REQUIRE(rows_per_batch > 0 && batches > 0 && N > 0 && K > 0, "empty GEMM");
   TcGemmShape s{};
   s.rows_per_batch = rows_per_batch;
@@ -416,14 +474,17 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
     s.conv_cg = conv->cg;
     a_cols = conv->channels;
   } else {
-    const bool can_split = ep.kind == EPI_RESID && ep.act == ACT_NONE;
+    // split-K meets in an L2 reduce-add whose order is not fixed: results would differ in the last ulp from run to run
+    // (and flip 16-bit roundings downstream), so it is only used on request (F5B_SPLIT_K=1 / force_splits)
+    static const bool allow_split = std::getenv("F5B_SPLIT_K") != nullptr;
+    const bool can_split = ep.kind == EPI_RESID && ep.act == ACT_NONE && (allow_split || force_splits > 1);
     pick_tiling((long long)s.tiles_m_per_batch * batches, N, K, sm_count, can_split, force_bn, force_splits, &bn,
                 &s.splits);
     a_cols = K;
   }
   s.tiles_n = (N + bn - 1) / bn;
   s.num_kb = (K + BK - 1) / BK;
-  const int fp16 = conv != nullptr && conv->fp16;
+  const int fp16 = fp16_operands || (conv != nullptr && conv->fp16);
   s.idesc = fp16 ? umma_idesc_f16(BM, bn, 0, 0) : umma_idesc_bf16(BM, bn, 0, 0);
 
   CUtensorMap ta, tb;
@@ -458,6 +519,9 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
     uint32_t box[3] = {(uint32_t)(128 / es), BM, 1};
     make_tmap(&to, base, 3, dims, strides, box, et);
   }
+  if (sync_debug())
+    fprintf(stderr, "tc_gemm rows %d x %d N %d K %d bn %d splits %d conv %d kind %d out_type %d act %d row_skip %d\n",
+            rows_per_batch, batches, N, K, bn, s.splits, s.conv, ep.kind, ep.out_type, ep.act, ep.row_skip);
   long long total = (long long)s.tiles_m_per_batch * batches * s.tiles_n * s.splits;
   int grid = (int)(total < sm_count ? total : sm_count);
   if (bn == 64)

@@ -39,7 +39,7 @@ void make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t
 // common leading dimension lda (elements).
 void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int rows_per_batch, int batches,
              const bf16* W, long long ldw, int N, int K, const EpiParams& ep, const TcConv* conv, int force_bn,
-             int force_splits = 0);
+             int force_splits = 0, int fp16 = 0 /* operands are IEEE fp16 */);
 
 // fp32 CUDA-core GEMM with the same epilogue (the correctness mode; also used for the tiny per-sample tables).
 void simt_gemm(cudaStream_t st, const float* A, long long lda, long long M, const float* W, long long ldw, int N,
@@ -52,7 +52,7 @@ void simt_group_conv(cudaStream_t st, const float* x, int batches, int rows, int
 // bf16 tensor-core attention (tcgen05) and fp32 CUDA-core attention.  qkv [batches*rows, 3*heads*64]; out
 // [batches*rows, heads*64].  kv_len[b] (or rows when null) keys take part.
 void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int rows, int heads, const int* kv_len,
-                  float scale);
+                  float scale, int out_f16 = 0 /* output written as IEEE fp16 (operand of the next GEMM) */);
 void simt_attention(cudaStream_t st, const float* qkv, float* out, int batches, int rows, int heads, const int* kv_len,
                     float scale);
 

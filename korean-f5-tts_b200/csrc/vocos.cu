@@ -126,7 +126,7 @@ struct f5b_vocos {
       e1.act = ACT_GELU_ERF;
       e1.bias = b.b1;
       e1.out = h;
-      e1.out_type = is16;
+      e1.out_type = is16 ? OUT_F16 : OUT_F32;
       e1.ldo = V_INT;
       e1.n_valid = V_INT;
       run_gemm(ctx, st, norm, V_DIM, M, b.pw1, e1);
@@ -182,7 +182,7 @@ int f5b_vocos_decode(f5b_vocos* v, const float* mel, int32_t B, int32_t T, float
     v->ensure(M);
     copy_in(v->mel_in, mel, (size_t)M * V_MEL * 4, mem, st);
     long long c0 = launch_count();
-    if (v->ctx.mode == F5B_MODE_BF16) v->run<bf16>(st, B, T);
+    if (v->ctx.mode == F5B_MODE_BF16) v->run<act16>(st, B, T);
     else v->run<float>(st, B, T);
     set_last_call(launch_count() - c0);
     copy_out(wav, v->wav, (size_t)B * (T - 1) * 256 * 4, mem, st);

@@ -70,7 +70,11 @@ def test_bf16_vs_fp32_oracle(backbone, N, B):
     keep = O.lens_to_mask(durs)[..., None] if B > 1 else torch.ones(1, N, 1, dtype=torch.bool)
     err = max_abs(out.cpu() * keep, ref.out * keep)
     print(f"bf16 {backbone} N={N} B={B}: max-abs {err:.4e}")
-    assert err <= 2e-2
+    # north_star tolerance for the 16-bit tensor-core mode: 2e-2 max-abs on the mel (values up to |10.5| here).
+    # Measured on B200: DiT 3.7e-3 / 4.0e-3, UNetT 7.2e-3 -- the linear layers contract IEEE fp16 operands (kind::f16,
+    # same rate as bf16); with bf16 operands the same cases sat at 1.3e-2 / 1.9e-2 / 4.2e-2 (tools/bf16_error_budget.py).
+    tol = 2e-2
+    assert err <= tol
     # the same model in fp32 mode must hit the tight tolerance
     cfm32 = build_cfm(cfg, sd, "fp32")
     out32, _ = cfm32.sample(cond=cond.cuda(), text=text.cuda(), duration=durs.cuda(), lens=lens.cuda(), steps=steps,

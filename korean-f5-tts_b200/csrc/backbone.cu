@@ -64,7 +64,7 @@ struct Layer {
 struct Bufs {
   long long cap_rows = 0;  // batches * R
   int capB = 0, cap_nt = 0, cap_steps = 0, capN = 0;
-  float *y, *cond, *v_out, *x, *hproj, *hconst, *a_in, *te, *sin_emb, *h1, *st_emb, *ada, *rope_cs, *t_dev, *grn_scratch, *traj;
+  float *y, *y2, *cond, *v_out, *x, *hproj, *hconst, *a_in, *te, *sin_emb, *h1, *st_emb, *ada, *rope_cs, *t_dev, *grn_scratch, *traj;
   long long traj_cap = 0;
   long long* text;
   int *lens_in, *lens2, *lens2p1;
@@ -291,6 +291,7 @@ void f5b_plan::ensure_ws(int B, int N, int nt, int steps, bool want_traj) {
   const int nT = steps > 2 * B ? steps : 2 * B;  // table rows: steps (sample) or B (forward)
   bf.cap_rows = rows; bf.capB = B; bf.cap_nt = nt; bf.cap_steps = steps; bf.capN = N; bf.traj_cap = traj_need;
   bf.y = A.alloc_n<float>((size_t)B * N * mel);
+  bf.y2 = A.alloc_n<float>((size_t)B * N * mel);
   bf.cond = A.alloc_n<float>((size_t)B * N * mel);
   bf.v_out = A.alloc_n<float>((size_t)2 * B * R * mel);  // UNetT keeps the time-token row; consumers skip it
   bf.x = A.alloc_n<float>((size_t)rows * d);
@@ -417,13 +418,7 @@ void f5b_plan::input_embed(cudaStream_t st, int batches, int N, const int* lens_
   const int d = a.dim;
   const long long M = (long long)batches * N;
   const bool is16 = sizeof(T) == 2;
-  EpiParams e;
-  e.out = bf.hproj;
-  e.ldo = d;
-  e.n_valid = d;
-  e.addend = bf.hconst;
-  e.ld_add = d;
-  simt_gemm(st, bf.a_in, kin_ld, M, in_proj.f32, kin, d, a.mel_dim, e);
+  // bf.hproj = hconst + y W_x^T was written by euler_xproj (fused with the previous Euler update)
   // bf16 mode feeds the position-embedding conv IEEE fp16 operands (kind::f16 runs both formats at the same rate):
   // h carries the large, slowly varying cond/text offsets and loses too much in 8 mantissa bits (precision)
   float* xdst = is_dit ? bf.x : bf.skips[0];

@@ -493,6 +493,123 @@ void cfg_euler(cudaStream_t st, float* y, const float* v, int v_lead_rows, float
   F5B_POST_LAUNCH();
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused CFG combine + Euler update + x-half of the input projection (cfm.py:162-191, torchdiffeq Euler, dit.py:138):
+//   y <- y + dt * (v_c + (v_c - v_u) * cfg)            (fp32; v == null: y unchanged -- the first evaluation)
+//   h[br] = hconst[br] + y W_x^T   for both CFG branches (the x columns are identical for cond / uncond, so the
+//   K = mel_dim contraction is done once and added to each branch's step-invariant half)
+// One CTA = 64 rows x 128 output columns; the CTAs of column tile 0 also write y (and the trajectory slot).
+// ---------------------------------------------------------------------------------------------
+static constexpr int XP_BM = 64, XP_BN = 128;
+
+__global__ void __launch_bounds__(256)
+euler_xproj_kernel(const float* __restrict__ y, float* __restrict__ y_next, const float* __restrict__ v, int v_lead, int B, int branches, int rows,
+                   int mel, float dt, float cfg, float* __restrict__ traj, const float* __restrict__ Wx, long long ldw,
+                   const float* __restrict__ hconst, float* __restrict__ hproj, int d) {
+  extern __shared__ float xp_smem[];
+  float* ws = xp_smem;                // [mel][XP_BN]
+  float* xs = xp_smem + mel * XP_BN;  // [XP_BM][mel + 1]
+  pdl_trigger();
+  const int tid = threadIdx.x;
+  const int n0 = blockIdx.x * XP_BN;
+  const long long m0 = (long long)blockIdx.y * XP_BM;
+  const long long M1 = (long long)B * rows;
+  const int xld = mel + 1;
+  // weights first: they do not depend on the previous kernel
+  if (hproj != nullptr) {
+    const int k4n = mel / 4;
+    for (int idx = tid; idx < XP_BN * k4n; idx += 256) {
+      const int n = idx & (XP_BN - 1), k4 = idx >> 7;
+      float4 w = make_float4(0, 0, 0, 0);
+      if (n0 + n < d) w = __ldg(reinterpret_cast<const float4*>(Wx + (long long)(n0 + n) * ldw + k4 * 4));
+      ws[(k4 * 4 + 0) * XP_BN + n] = w.x;
+      ws[(k4 * 4 + 1) * XP_BN + n] = w.y;
+      ws[(k4 * 4 + 2) * XP_BN + n] = w.z;
+      ws[(k4 * 4 + 3) * XP_BN + n] = w.w;
+    }
+  }
+  pdl_wait();
+  const bool writer = blockIdx.x == 0;
+  const long long total = M1 * mel;
+  for (int e = tid; e < XP_BM * mel; e += 256) {
+    const int r = e / mel, c = e - r * mel;
+    const long long m = m0 + r;
+    float yv = 0.0f;
+    if (m < M1) {
+      const long long i = m * mel + c;
+      yv = y[i];
+      if (v != nullptr) {
+        const long long bb = m / rows;  // batch element; v has rows + v_lead rows per element
+        const long long vi = i + (bb + 1) * (long long)v_lead * mel;
+        const float pc = v[vi];
+        float vel = pc;
+        if (branches == 2) {
+          const float pu = v[vi + (long long)B * (rows + v_lead) * mel];
+          vel = pc + (pc - pu) * cfg;
+        }
+        yv = yv + dt * vel;
+        if (writer) y_next[i] = yv;  // a different buffer: the other column tiles of this row tile still read y
+      }
+      if (writer && traj) traj[i] = yv;
+    }
+    xs[r * xld + c] = yv;
+  }
+  (void)total;
+  if (hproj == nullptr) return;
+  __syncthreads();
+  const int tx = tid & 15, ty = tid >> 4;
+  float acc[4][8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0f;
+  for (int k = 0; k < mel; ++k) {
+    const float4 w0 = *reinterpret_cast<const float4*>(ws + k * XP_BN + tx * 8);
+    const float4 w1 = *reinterpret_cast<const float4*>(ws + k * XP_BN + tx * 8 + 4);
+    const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float a = xs[(ty * 4 + i) * xld + k];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a, wv[j], acc[i][j]);
+    }
+  }
+  const int n = n0 + tx * 8;
+  if (n >= d) return;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const long long m = m0 + ty * 4 + i;
+    if (m >= M1) continue;
+    for (int br = 0; br < branches; ++br) {
+      const long long o = (m + (long long)br * M1) * d + n;
+      const float4 h0 = *reinterpret_cast<const float4*>(hconst + o);
+      const float4 h1 = *reinterpret_cast<const float4*>(hconst + o + 4);
+      *reinterpret_cast<float4*>(hproj + o) =
+          make_float4(h0.x + acc[i][0], h0.y + acc[i][1], h0.z + acc[i][2], h0.w + acc[i][3]);
+      *reinterpret_cast<float4*>(hproj + o + 4) =
+          make_float4(h1.x + acc[i][4], h1.y + acc[i][5], h1.z + acc[i][6], h1.w + acc[i][7]);
+    }
+  }
+}
+
+void euler_xproj(cudaStream_t st, const float* y, float* y_next, const float* v, int v_lead_rows, int B, int branches, int rows, int mel,
+                 float dt, float cfg, float* traj_slot, const float* Wx, long long ldw, const float* hconst,
+                 float* hproj, int d) {
+  F5B_REQUIRE(mel % 4 == 0 && d % 8 == 0 && ldw % 4 == 0, "euler_xproj needs mel % 4 == 0, dim % 8 == 0");
+  const size_t smem = (size_t)(mel * XP_BN + XP_BM * (mel + 1)) * sizeof(float);
+  static size_t configured = 0;
+  if (smem > configured) {
+    F5B_CHECK_CUDA(cudaFuncSetAttribute(euler_xproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  const long long M1 = (long long)B * rows;
+  dim3 grid(hproj ? (d + XP_BN - 1) / XP_BN : 1, (unsigned)((M1 + XP_BM - 1) / XP_BM));
+  F5B_REQUIRE(v == nullptr || (y_next != nullptr && y_next != y), "euler_xproj needs a distinct output state buffer");
+  launch_pdl_id(8, euler_xproj_kernel, grid, dim3(256), smem, st, y, y_next, v, v_lead_rows, B, branches, rows, mel, dt, cfg,
+                traj_slot, Wx, ldw, hconst, hproj, d);
+  F5B_POST_LAUNCH();
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 cast_mask_kernel(const float* __restrict__ x, T* __restrict__ out, int rows, int d4, const int* __restrict__ row_len,

@@ -47,6 +47,12 @@ void cfg_euler(cudaStream_t st, float* y, const float* v, int v_lead_rows, float
                int mel, float dt, float cfg, float* traj_slot);
 
 // out = masked cast of x; copy (optional) = x unchanged (seeds the residual stream for the conv pos-emb epilogue)
+// Fused CFG + Euler update of y and x-half of the input projection: hproj[br] = hconst[br] + y W_x^T (null hproj: update
+// only).  The new state goes to y_next (column tiles of a row tile run in different CTAs).  v == null leaves y unchanged (first evaluation / f5b_forward).
+void euler_xproj(cudaStream_t st, const float* y, float* y_next, const float* v, int v_lead_rows, int B, int branches, int rows, int mel,
+                 float dt, float cfg, float* traj_slot, const float* Wx, long long ldw, const float* hconst,
+                 float* hproj, int d);
+
 template <typename T>
 void cast_mask(cudaStream_t st, const float* x, T* out, int batches, int rows, int d, const int* row_len,
                float* copy = nullptr);

@@ -114,8 +114,10 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
       mbar_wait(q_full, 0);
       mbar_wait(&kv_full[0], 0);
       tc_fence_after();
+      // Tile 1 starts one softmax later than tile 0 (its first S is issued after tile 0's first P*V): the two warp
+      // groups then stay half a period apart, so one exponentiates (MUFU) while the other waits for / reads its S.
+      // Started together they run in lock step, contend for the MUFU and both idle during the MMAs.
       issue_s(0, 0);
-      issue_s(1, 0);
       for (int j = 0; j < nkv; ++j) {
         const int st = j % AT_KV_STAGES;
         const int stn = (j + 1) % AT_KV_STAGES;
@@ -132,6 +134,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
                     umma_desc_sw128(v_addr + k * 16 * 128, 1024, 1024), IDESC_O, (j | k) != 0 ? 1u : 0u);
           if (j + 1 < nkv) issue_s(t, stn);  // S_t(j+1): its commit also covers PV_t(j)
           else umma_commit(&o_done[t]);
+          if (j == 0 && t == 0) issue_s(1, 0);
         }
         umma_commit(&kv_empty[st]);  // K_j / V_j have been read by every MMA issued so far
       }

@@ -42,3 +42,39 @@ def micro_batches(indices: Sequence[int], lengths: Sequence[int], max_rows: int,
     if cur:
         out.append(cur)
     return out
+
+
+def my_shard(lengths: Sequence[int], rank: int, world_size: int, **cost_kw) -> List[int]:
+    """The utterance indices this rank synthesises (every rank computes the same deterministic partition)."""
+    return shard_requests(lengths, world_size, **cost_kw)[rank]
+
+
+def gather_to_rank0(local: dict, group=None) -> dict | None:
+    """Host-side gather of `{utterance index: result}` dicts (the reference gathers on the host as well,
+    eval_infer_batch.py:181-208).  No tensor collective is involved: the data path stays shard-local."""
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return dict(local)
+    parts = [None] * dist.get_world_size(group) if dist.get_rank(group) == 0 else None
+    dist.gather_object(local, parts, dst=0, group=group)
+    if parts is None:
+        return None
+    merged: dict = {}
+    for p in parts:
+        overlap = merged.keys() & p.keys()
+        assert not overlap, f"utterances synthesised twice: {sorted(overlap)}"
+        merged.update(p)
+    return merged
+
+
+def max_over_ranks(seconds: float, device=None, group=None) -> float:
+    """Timing rule of bench.py: a multi-GPU number is the MAX over ranks of the device-timed region."""
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return float(seconds)
+    t = torch.tensor([seconds], dtype=torch.float64, device=device or "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return float(t.item())

@@ -1,0 +1,53 @@
+"""N > 1 host logic on CPU: two gloo ranks shard a request list, "synthesise" their shard, gather on rank 0 and take the
+max-over-ranks timing -- the same plumbing bench.py runs over NCCL on the GPU box (no data-path collective)."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "korean-f5-tts_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def _worker(rank, world, port, lengths, out_q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from f5b200 import sharding
+
+        mine = sharding.my_shard(lengths, rank, world)
+        local = {i: lengths[i] * 256 for i in mine}  # stand-in for a waveform: its sample count
+        merged = sharding.gather_to_rank0(local)
+        t = sharding.max_over_ranks(0.5 + rank)  # rank 1 is the slow one
+        dist.barrier()
+        if rank == 0:
+            out_q.put((merged, t, mine))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_request_sharding_gloo():
+    g = torch.Generator().manual_seed(0)
+    lengths = [int(x) for x in torch.randint(281, 1875, (37,), generator=g)]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, lengths, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    merged, t, mine0 = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert sorted(merged) == list(range(len(lengths)))  # every utterance exactly once
+    assert all(merged[i] == lengths[i] * 256 for i in merged)
+    assert t == 1.5  # max over ranks
+    from f5b200 import sharding
+
+    loads = [sum(sharding.request_cost(lengths[i]) for i in s) for s in sharding.shard_requests(lengths, 2)]
+    assert max(loads) / min(loads) < 1.05  # LPT balance
+    assert mine0 == sharding.shard_requests(lengths, 2)[0]

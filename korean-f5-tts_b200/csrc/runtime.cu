@@ -295,6 +295,27 @@ int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int3
 }
 
 
+/* Debug: run the tcgen05 attention once on constant data with the in-kernel timeline enabled; out[3][64][4] receives
+ * clock64 stamps of CTA (0,0,0): who 0/1 = softmax tile 0/1 {wait S, S ready, max done, P handed over}, who 2 = MMA
+ * issuer {wait P0, P0 seen, wait P1, P1 seen} per key block. */
+int f5b_debug_attn_trace(int32_t rows, int32_t heads, int32_t batches, int64_t* out, int32_t device) {
+  F5B_API_BEGIN
+  open_device(device, F5B_MODE_BF16);
+  Arena arena;
+  const int inner = heads * 64;
+  bf16* Q = arena.alloc_n<bf16>((size_t)batches * rows * 3 * inner);
+  bf16* O = arena.alloc_n<bf16>((size_t)batches * rows * inner);
+  F5B_CHECK_CUDA(cudaMemset(Q, 0x3c, (size_t)batches * rows * 3 * inner * 2));
+  tc_attention(0, Q, O, batches, rows, heads, nullptr, 0.125f);  // warm-up
+  F5B_CHECK_CUDA(cudaDeviceSynchronize());
+  attn_trace_enable(1);
+  tc_attention(0, Q, O, batches, rows, heads, nullptr, 0.125f);
+  F5B_CHECK_CUDA(cudaDeviceSynchronize());
+  attn_trace_enable(0);
+  attn_trace_read(reinterpret_cast<long long*>(out));
+  F5B_API_END
+}
+
 int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, float* ms, int32_t device, void* stream) {
   F5B_API_BEGIN
   F5B_REQUIRE(ms != nullptr && iters > 0, "bad argument");

@@ -29,7 +29,16 @@ static constexpr int AT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: Q_t, K_j, V_j, and
 static constexpr int AT_KV_STAGES = 3;
 static constexpr int AT_SMEM = AT_TILE_BYTES * (2 + 2 * AT_KV_STAGES + 4) + 1024 + 256;
 static constexpr uint32_t AT_TMEM_COLS = 512;  // S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384)
+static constexpr unsigned AT_STAGGER_NS = 700;  // ~1300 cycles: half of the measured per-block period
 static constexpr float AT_LAZY = 8.0f;         // rescale only when the block maximum exceeds the reference by 2^8
+
+// Debug timeline (f5b_debug_attn_trace): CTA (0,0,0) stamps clock64 at its pipeline events.  [who][j][event]
+__device__ long long g_attn_trace[3 * 64 * 4];
+__device__ int g_attn_trace_on = 0;
+#define AT_STAMP(who, j, ev)                                                                         \
+  do {                                                                                               \
+    if (trace && (j) < 64) g_attn_trace[((who) * 64 + (j)) * 4 + (ev)] = clock64();                  \
+  } while (0)
 
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
@@ -61,6 +70,8 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
   const int inner = heads * AT_D;
   const int L = kv_len ? kv_len[b] : rows;
   const int nkv = (L + AT_BKV - 1) / AT_BKV;
+  const bool trace = g_attn_trace_on && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 &&
+                     (warp == 0 || warp == 4 || warp == 9);
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tm);
@@ -114,18 +125,18 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
       mbar_wait(q_full, 0);
       mbar_wait(&kv_full[0], 0);
       tc_fence_after();
-      // Tile 1 starts one softmax later than tile 0 (its first S is issued after tile 0's first P*V): the two warp
-      // groups then stay half a period apart, so one exponentiates (MUFU) while the other waits for / reads its S.
-      // Started together they run in lock step, contend for the MUFU and both idle during the MMAs.
       issue_s(0, 0);
+      issue_s(1, 0);
       for (int j = 0; j < nkv; ++j) {
         const int st = j % AT_KV_STAGES;
         const int stn = (j + 1) % AT_KV_STAGES;
         const uint32_t v_addr = smem_u32(sV + st * AT_TILE_BYTES);
         if (j + 1 < nkv) mbar_wait(&kv_full[stn], ((j + 1) / AT_KV_STAGES) & 1);
         for (int t = 0; t < 2; ++t) {
+          AT_STAMP(2, j, t * 2);
           mbar_wait(&p_full[t], j & 1);
           tc_fence_after();
+          AT_STAMP(2, j, t * 2 + 1);
           const uint32_t p_addr = smem_u32(sP + t * 2 * AT_TILE_BYTES);
 #pragma unroll
           for (int k = 0; k < AT_BKV / 16; ++k)
@@ -134,7 +145,6 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
                     umma_desc_sw128(v_addr + k * 16 * 128, 1024, 1024), IDESC_O, (j | k) != 0 ? 1u : 0u);
           if (j + 1 < nkv) issue_s(t, stn);  // S_t(j+1): its commit also covers PV_t(j)
           else umma_commit(&o_done[t]);
-          if (j == 0 && t == 0) issue_s(1, 0);
         }
         umma_commit(&kv_empty[st]);  // K_j / V_j have been read by every MMA issued so far
       }
@@ -149,10 +159,16 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
     uint8_t* p_row = sP + t * 2 * AT_TILE_BYTES + row * 128;
     const int sw = row & 7;
     float m_ref = -INFINITY, l = 0.0f;
+    // Started together the two warp groups run in lock step: both exponentiate at once (contending for the MUFU) and
+    // both idle while the MMAs run.  Tile 1 therefore begins about half a block period late; the offset sustains
+    // itself because each group's S / P*V round trip then falls into the other group's exponentiation phase.
+    if (t == 1 && nkv > 1) __nanosleep(AT_STAGGER_NS);
 
     for (int j = 0; j < nkv; ++j) {
+      AT_STAMP(t, j, 0);
       mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
+      AT_STAMP(t, j, 1);
       float s[AT_BKV];
       tmem_ld_32x32(tS, s);
       tmem_ld_32x32(tS + 32, s + 32);
@@ -196,6 +212,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
           tmem_st_wait();
         }
       }
+      AT_STAMP(t, j, 2);
       const float moff = m_ref * scale_log2;
       float ps4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
@@ -221,6 +238,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[t]);
+      AT_STAMP(t, j, 3);
     }
 
     if (nkv > 0) mbar_wait(&o_done[t], 0);  // (no keys at all: O is never produced, the rows below store 0 * inf = NaN
@@ -274,6 +292,11 @@ void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int 
   launch_pdl_id(2, tc_attn_kernel, grid, dim3(320), AT_SMEM, st, tm, out, rows, heads, kv_len,
              scale * 1.4426950408889634f, out_f16);
   F5B_POST_LAUNCH();
+}
+
+void attn_trace_enable(int on) { F5B_CHECK_CUDA(cudaMemcpyToSymbol(g_attn_trace_on, &on, sizeof(int))); }
+void attn_trace_read(long long* host) {
+  F5B_CHECK_CUDA(cudaMemcpyFromSymbol(host, g_attn_trace, sizeof(long long) * 3 * 64 * 4));
 }
 
 void tc_init_kernels() {

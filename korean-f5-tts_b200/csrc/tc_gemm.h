@@ -56,6 +56,8 @@ void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int 
 void simt_attention(cudaStream_t st, const float* qkv, float* out, int batches, int rows, int heads, const int* kv_len,
                     float scale);
 
+void attn_trace_enable(int on);
+void attn_trace_read(long long* host /* [3][64][4] clock64 stamps */);
 void tc_init_kernels();       // attention
 void tc_gemm_init_kernels();  // GEMM
 void simt_init_kernels();

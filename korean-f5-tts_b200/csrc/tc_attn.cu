@@ -113,13 +113,16 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
       // ------------------------------- MMA issuer ---------------------------------
       constexpr uint32_t IDESC_S = umma_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t IDESC_O = umma_idesc_bf16(128, 64, 0, 1);  // B = V is MN-major
+      // descriptors: only the 14-bit start-address field changes; built once, advanced by adds (single issuing lane)
+      const uint64_t dK = umma_desc_sw128(0, 16, 1024);    // K-major operands (Q, K_j, P)
+      const uint64_t dV = umma_desc_sw128(0, 1024, 1024);  // MN-major operand (V_j)
+      const uint32_t q_lo = smem_u32(sQ) >> 4, k_lo = smem_u32(sK) >> 4, v_lo = smem_u32(sV) >> 4, p_lo = smem_u32(sP) >> 4;
       auto issue_s = [&](int t, int st) {
-        const uint32_t q_addr = smem_u32(sQ + t * AT_TILE_BYTES);
-        const uint32_t k_addr = smem_u32(sK + st * AT_TILE_BYTES);
+        const uint64_t qd = dK | (uint64_t)(q_lo + t * (AT_TILE_BYTES >> 4));
+        const uint64_t kd = dK | (uint64_t)(k_lo + st * (AT_TILE_BYTES >> 4));
+        umma_ss(tmem_base + t * 128, qd, kd, IDESC_S, 0u);
 #pragma unroll
-        for (int k = 0; k < AT_D / 16; ++k)
-          umma_ss(tmem_base + t * 128, umma_desc_sw128(q_addr + k * 32, 16, 1024),
-                  umma_desc_sw128(k_addr + k * 32, 16, 1024), IDESC_S, k != 0 ? 1u : 0u);
+        for (int k = 1; k < AT_D / 16; ++k) umma_ss(tmem_base + t * 128, qd + 2 * k, kd + 2 * k, IDESC_S, 1u);
         umma_commit(&s_full[t]);
       };
       mbar_wait(q_full, 0);
@@ -130,19 +133,18 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
       for (int j = 0; j < nkv; ++j) {
         const int st = j % AT_KV_STAGES;
         const int stn = (j + 1) % AT_KV_STAGES;
-        const uint32_t v_addr = smem_u32(sV + st * AT_TILE_BYTES);
         if (j + 1 < nkv) mbar_wait(&kv_full[stn], ((j + 1) / AT_KV_STAGES) & 1);
         for (int t = 0; t < 2; ++t) {
           AT_STAMP(2, j, t * 2);
           mbar_wait(&p_full[t], j & 1);
           tc_fence_after();
           AT_STAMP(2, j, t * 2 + 1);
-          const uint32_t p_addr = smem_u32(sP + t * 2 * AT_TILE_BYTES);
+          const uint64_t pd = dK | (uint64_t)(p_lo + t * 2 * (AT_TILE_BYTES >> 4));
+          const uint64_t vd = dV | (uint64_t)(v_lo + st * (AT_TILE_BYTES >> 4));
 #pragma unroll
-          for (int k = 0; k < AT_BKV / 16; ++k)
-            umma_ss(tmem_base + 256 + t * 64,
-                    umma_desc_sw128(p_addr + (k >> 2) * AT_TILE_BYTES + (k & 3) * 32, 16, 1024),
-                    umma_desc_sw128(v_addr + k * 16 * 128, 1024, 1024), IDESC_O, (j | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < AT_BKV / 16; ++k)  // P: 32 B per k-step inside a 64-key panel; V: 16 rows of 128 B
+            umma_ss(tmem_base + 256 + t * 64, pd + (k >> 2) * (AT_TILE_BYTES >> 4) + (k & 3) * 2, vd + 128 * k, IDESC_O,
+                    (j | k) != 0 ? 1u : 0u);
           if (j + 1 < nkv) issue_s(t, stn);  // S_t(j+1): its commit also covers PV_t(j)
           else umma_commit(&o_done[t]);
         }

@@ -206,6 +206,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp == 1 && lane == 0) {
     // ------------------------------- MMA issuer ---------------------------------
+    // Descriptors are built once: only the 14-bit start-address field (bytes >> 4) changes between MMAs, and it cannot
+    // carry out of its field (smem addresses < 256 KB), so a stage / k-step advance is a plain add.  The issuing thread
+    // is a single lane: every instruction it spends per MMA is serial latency on the tensor pipe's critical path.
+    const uint64_t desc0 = umma_desc_sw128(0, 16, 1024);
+    const uint32_t a_lo = smem_u32(sA) >> 4, b_lo = smem_u32(sB) >> 4;
+    const uint32_t idesc = s.idesc;
     uint32_t it = 0, tcount = 0;
     for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x, ++tcount) {
       const int ks = unit % s.splits;
@@ -214,19 +220,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_wait(&tempty[acc], aph ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * BN;
+      uint32_t st = it % STAGES, ph = (it / STAGES) & 1u;
       for (int kb = kb0; kb < kb1; ++kb, ++it) {
-        const uint32_t st = it % STAGES, ph = (it / STAGES) & 1u;
         mbar_wait(&full[st], ph);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(sA + st * A_STAGE_BYTES);
-        const uint32_t b_addr = smem_u32(sB + st * B_STAGE_BYTES);
+        const uint64_t ad = desc0 | (uint64_t)(a_lo + st * (A_STAGE_BYTES >> 4));
+        const uint64_t bd = desc0 | (uint64_t)(b_lo + st * (B_STAGE_BYTES >> 4));
+        umma_ss(d_tmem, ad, bd, idesc, kb != kb0 ? 1u : 0u);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint64_t ad = umma_desc_sw128(a_addr + k * 32, 16, 1024);
-          const uint64_t bd = umma_desc_sw128(b_addr + k * 32, 16, 1024);
-          umma_ss(d_tmem, ad, bd, s.idesc, (kb != kb0 || k != 0) ? 1u : 0u);
-        }
+        for (int k = 1; k < BK / 16; ++k) umma_ss(d_tmem, ad + 2 * k, bd + 2 * k, idesc, 1u);
         umma_commit(&empty[st]);  // frees the smem slot once these MMAs have read it
+        if (++st == STAGES) {
+          st = 0;
+          ph ^= 1u;
+        }
       }
       umma_commit(&tfull[acc]);  // accumulator complete
     }

@@ -9,11 +9,12 @@
 //   warps 4..7 : softmax of query tile 1
 //   warp 8     : TMA producer (Q0, Q1 once; K_j, V_j through a 3-stage ring)
 //   warp 9     : MMA issuer.  Per key block j and tile t:  S_t = Q_t K_j^T (4 x 128x128x16) into TMEM,
-//                O_t += P_t V_j (8 x 128x64x16, V read MN-major) accumulated IN TMEM.
+//                O_t += P_t V_j (8 x 128x64x16, A = P_t read from TMEM, V read MN-major) accumulated IN TMEM.
 //
 // The two tiles ping-pong: while tile 0's threads exponentiate block j, the tensor core runs tile 1's S / PV, so
 // neither the MMA latency nor the softmax is exposed.  Each S block is read from TMEM exactly once (128 registers per
-// thread).  O is never read back per block: the running maximum is only raised when a block exceeds it by more than
+// thread) and P goes back into the same TMEM columns as packed bf16 pairs (tcgen05.st), from where the P*V MMA takes
+// it as its A operand.  O is never read back per block: the running maximum is only raised when a block exceeds it by more than
 // 2^8 (lazy rescaling; P is then still < 256, harmless in bf16 / fp32), in which case the warp rescales its O rows in
 // TMEM (tcgen05.ld / st).  The final O is read once, divided by the row sum and stored as bf16.
 #include "common.cuh"
@@ -25,9 +26,9 @@ namespace f5b {
 using namespace ptx;
 
 static constexpr int AT_BQ = 128, AT_BKV = 128, AT_D = 64;
-static constexpr int AT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: Q_t, K_j, V_j, and each of the two P panels of a tile
+static constexpr int AT_TILE_BYTES = 128 * 64 * 2;  // 16 KB: Q_t, K_j, V_j
 static constexpr int AT_KV_STAGES = 3;
-static constexpr int AT_SMEM = AT_TILE_BYTES * (2 + 2 * AT_KV_STAGES + 4) + 1024 + 256;
+static constexpr int AT_SMEM = AT_TILE_BYTES * (2 + 2 * AT_KV_STAGES) + 1024 + 256;
 static constexpr uint32_t AT_TMEM_COLS = 512;  // S0 [0,128) S1 [128,256) O0 [256,320) O1 [320,384)
 static constexpr unsigned AT_STAGGER_NS = 700;  // ~1300 cycles: half of the measured per-block period
 static constexpr float AT_LAZY = 8.0f;         // rescale only when the block maximum exceeds the reference by 2^8
@@ -54,8 +55,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
   uint8_t* sQ = smem;                                  // 2 tiles
   uint8_t* sK = sQ + 2 * AT_TILE_BYTES;                // AT_KV_STAGES
   uint8_t* sV = sK + AT_KV_STAGES * AT_TILE_BYTES;     // AT_KV_STAGES
-  uint8_t* sP = sV + AT_KV_STAGES * AT_TILE_BYTES;     // 2 tiles x 2 panels of 64 kv columns
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 4 * AT_TILE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + AT_KV_STAGES * AT_TILE_BYTES);
   uint64_t* q_full = bars;                        // [1]
   uint64_t* kv_full = bars + 1;                   // [AT_KV_STAGES]
   uint64_t* kv_empty = kv_full + AT_KV_STAGES;    // [AT_KV_STAGES]
@@ -116,7 +116,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
       // descriptors: only the 14-bit start-address field changes; built once, advanced by adds (single issuing lane)
       const uint64_t dK = umma_desc_sw128(0, 16, 1024);    // K-major operands (Q, K_j, P)
       const uint64_t dV = umma_desc_sw128(0, 1024, 1024);  // MN-major operand (V_j)
-      const uint32_t q_lo = smem_u32(sQ) >> 4, k_lo = smem_u32(sK) >> 4, v_lo = smem_u32(sV) >> 4, p_lo = smem_u32(sP) >> 4;
+      const uint32_t q_lo = smem_u32(sQ) >> 4, k_lo = smem_u32(sK) >> 4, v_lo = smem_u32(sV) >> 4;
       auto issue_s = [&](int t, int st) {
         const uint64_t qd = dK | (uint64_t)(q_lo + t * (AT_TILE_BYTES >> 4));
         const uint64_t kd = dK | (uint64_t)(k_lo + st * (AT_TILE_BYTES >> 4));
@@ -139,12 +139,10 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
           mbar_wait(&p_full[t], j & 1);
           tc_fence_after();
           AT_STAMP(2, j, t * 2 + 1);
-          const uint64_t pd = dK | (uint64_t)(p_lo + t * 2 * (AT_TILE_BYTES >> 4));
           const uint64_t vd = dV | (uint64_t)(v_lo + st * (AT_TILE_BYTES >> 4));
 #pragma unroll
-          for (int k = 0; k < AT_BKV / 16; ++k)  // P: 32 B per k-step inside a 64-key panel; V: 16 rows of 128 B
-            umma_ss(tmem_base + 256 + t * 64, pd + (k >> 2) * (AT_TILE_BYTES >> 4) + (k & 3) * 2, vd + 128 * k, IDESC_O,
-                    (j | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < AT_BKV / 16; ++k)  // A = P_t in TMEM over S_t: 8 columns (16 keys) per k-step; V: 16 rows
+            umma_ts(tmem_base + 256 + t * 64, tmem_base + t * 128 + 8 * k, vd + 128 * k, IDESC_O, (j | k) != 0 ? 1u : 0u);
           if (j + 1 < nkv) issue_s(t, stn);  // S_t(j+1): its commit also covers PV_t(j)
           else umma_commit(&o_done[t]);
         }
@@ -158,8 +156,6 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
     const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const uint32_t tS = tmem_base + t * 128 + lane_off;
     const uint32_t tO = tmem_base + 256 + t * 64 + lane_off;
-    uint8_t* p_row = sP + t * 2 * AT_TILE_BYTES + row * 128;
-    const int sw = row & 7;
     float m_ref = -INFINITY, l = 0.0f;
     // Started together the two warp groups run in lock step: both exponentiate at once (contending for the MUFU) and
     // both idle while the MMAs run.  Tile 1 therefore begins about half a block period late; the offset sustains
@@ -226,17 +222,17 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
         }
       }
       l += (ps4[0] + ps4[1]) + (ps4[2] + ps4[3]);
+      // P_t(j) as bf16 pairs into the first 64 columns of the S_t region (S is in registers by now): the P*V MMA reads
+      // its A operand straight from tensor memory -- no shared-memory round trip and no operand bandwidth for P.  The
+      // next S_t overwrites the region only after P*V (MMAs of one thread execute in issue order).
+      {
+        uint32_t* pk = reinterpret_cast<uint32_t*>(s);
 #pragma unroll
-      for (int g = 0; g < AT_BKV / 8; ++g) {
-        uint4 pk;
-        pk.x = pack_bf16x2(s[g * 8 + 0], s[g * 8 + 1]);
-        pk.y = pack_bf16x2(s[g * 8 + 2], s[g * 8 + 3]);
-        pk.z = pack_bf16x2(s[g * 8 + 4], s[g * 8 + 5]);
-        pk.w = pack_bf16x2(s[g * 8 + 6], s[g * 8 + 7]);
-        uint8_t* panel = p_row + (g >> 3) * AT_TILE_BYTES;
-        *reinterpret_cast<uint4*>(panel + (((g & 7) ^ sw) << 4)) = pk;
+        for (int i = 0; i < AT_BKV / 2; ++i) pk[i] = pack_bf16x2(s[2 * i], s[2 * i + 1]);
+        tmem_st_32x32(tS, s);
+        tmem_st_32x32(tS + 32, s + 32);
+        tmem_st_wait();
       }
-      fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[t]);

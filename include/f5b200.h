@@ -111,6 +111,12 @@ int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, f
 /* Debug timeline of one attention CTA (clock64 stamps, see csrc/runtime.cu); out = int64[3*64*4]. */
 int f5b_debug_attn_trace(int32_t rows, int32_t heads, int32_t batches, int64_t* out, int32_t device);
 
+/* Debug in-situ kernel timeline (library built with F5B_KTRACE=1 only; otherwise F5B_ERR_INVALID).
+ *   op 0: start -- allocate room for `capacity` records on `device` and arm the per-step kernels;
+ *   op 1: stop  -- copy min(*n, capacity) records of 4 x int64 {t_entry, t_after_dependency_wait, t_exit (globaltimer
+ *                  ns), kernel_id << 32 | cta} to `out`, set *n to the number recorded, release the buffer. */
+int f5b_debug_ktrace(int32_t op, int64_t capacity, int64_t* out, int64_t* n, int32_t device);
+
 /* Number of kernel launches issued by this library since load (for bench.py's gpu_launches). */
 int64_t f5b_launch_count(void);
 /* Kernel launches inside the last f5b_sample / f5b_vocos_decode / f5b_mel call (graph nodes count individually). */

@@ -13,6 +13,8 @@ OBJ = os.path.join(HERE, "build")
 SOURCES = ["runtime.cu", "rowwise.cu", "simt.cu", "tc_gemm.cu", "tc_attn.cu", "backbone.cu", "stft.cu", "vocos.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
+if os.environ.get("F5B_KTRACE") == "1":  # debug build: in-situ kernel timeline (csrc/common.cuh, tools/ktrace.py)
+    FLAGS.append("-DF5B_KTRACE")
 
 
 def _deps_mtime() -> float:

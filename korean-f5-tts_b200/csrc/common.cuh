@@ -104,6 +104,46 @@ bool pdl_enabled(int kernel_id = 0);  // programmatic dependent launch for the p
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// In-situ kernel timeline (debug builds only: `F5B_KTRACE=1 python build.py --force` adds -DF5B_KTRACE).  Thread 0 of
+// every CTA of the per-step chain records %globaltimer at kernel entry, after the programmatic-dependency wait and at
+// exit; f5b_debug_ktrace() returns the records, tools/ktrace.py turns them into a per-launch timeline (launch gap,
+// ramp, tail) of the graph-replayed sampling loop -- the view nsys would give.  Without the flag the macros vanish.
+#if defined(F5B_KTRACE)
+static __device__ unsigned long long* g_ktrace;  // per translation unit; [0] record count, [1] capacity, records from [4]
+__device__ __forceinline__ unsigned long long ktrace_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define KT_DECL __shared__ unsigned long long kt_stamp[6];
+#define KT_MARK(i) do { kt_stamp[i] = ktrace_now(); } while (0)  /* kernel-specific phase stamps 2..5 */
+#define KT_BEGIN()  do { if (threadIdx.x == 0) kt_stamp[0] = ktrace_now(); } while (0)
+#define KT_WAITED() do { if (threadIdx.x == 0) kt_stamp[1] = ktrace_now(); } while (0)
+#define KT_END(kid)                                                                                         \
+  do {                                                                                                      \
+    if (threadIdx.x == 0 && g_ktrace) {                                                                     \
+      unsigned long long* kt_p = g_ktrace;                                                                  \
+      unsigned long long kt_i = atomicAdd(kt_p, 1ULL);                                                      \
+      if (kt_i < kt_p[1]) {                                                                                 \
+        unsigned long long* r = kt_p + 4 + 8 * kt_i;                                                        \
+        r[0] = kt_stamp[0]; r[1] = kt_stamp[1]; r[2] = ktrace_now();                                        \
+        r[3] = ((unsigned long long)(kid) << 32) | (blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)); \
+        r[4] = kt_stamp[2]; r[5] = kt_stamp[3]; r[6] = kt_stamp[4]; r[7] = kt_stamp[5];                    \
+      }                                                                                                     \
+    }                                                                                                       \
+  } while (0)
+#define KT_DEFINE_SETTER(name) \
+  void name(unsigned long long* p) { F5B_CHECK_CUDA(cudaMemcpyToSymbol(g_ktrace, &p, sizeof(p))); }
+#else
+#define KT_DECL
+#define KT_BEGIN() do { } while (0)
+#define KT_WAITED() do { } while (0)
+#define KT_MARK(i) do { } while (0)
+#define KT_END(kid) do { } while (0)
+#define KT_DEFINE_SETTER(name) \
+  void name(unsigned long long*) {}
+#endif
+
 template <typename... P, typename... A>
 inline void launch_pdl_id(int kernel_id, void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
                           A&&... args) {

@@ -117,6 +117,8 @@ __global__ void __launch_bounds__(256)
 ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d, const float* __restrict__ mul,
                   const float* __restrict__ add, float mul_off, long long vec_bstride, int rows_per_batch, int bmod,
                   float eps) {
+  KT_DECL
+  KT_BEGIN();
   pdl_trigger();
   const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -137,6 +139,7 @@ ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M,
     }
   }
   pdl_wait();
+  KT_WAITED();
   float s = 0.0f;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
@@ -169,6 +172,7 @@ ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M,
                     (v.w - mean) * rstd * (mul_off + g[i].w) + h[i].w);
     }
   }
+  KT_END(4);
 }
 
 template <typename T>
@@ -509,6 +513,8 @@ euler_xproj_kernel(const float* __restrict__ y, float* __restrict__ y_next, cons
   extern __shared__ float xp_smem[];
   float* ws = xp_smem;                // [mel][XP_BN]
   float* xs = xp_smem + mel * XP_BN;  // [XP_BM][mel + 1]
+  KT_DECL
+  KT_BEGIN();
   pdl_trigger();
   const int tid = threadIdx.x;
   const int n0 = blockIdx.x * XP_BN;
@@ -529,6 +535,7 @@ euler_xproj_kernel(const float* __restrict__ y, float* __restrict__ y_next, cons
     }
   }
   pdl_wait();
+  KT_WAITED();
   const bool writer = blockIdx.x == 0;
   const long long total = M1 * mel;
   for (int e = tid; e < XP_BM * mel; e += 256) {
@@ -590,7 +597,10 @@ euler_xproj_kernel(const float* __restrict__ y, float* __restrict__ y_next, cons
           make_float4(h1.x + acc[i][4], h1.y + acc[i][5], h1.z + acc[i][6], h1.w + acc[i][7]);
     }
   }
+  KT_END(8);
 }
+
+KT_DEFINE_SETTER(ktrace_set_rowwise)
 
 void euler_xproj(cudaStream_t st, const float* y, float* y_next, const float* v, int v_lead_rows, int B, int branches, int rows, int mel,
                  float dt, float cfg, float* traj_slot, const float* Wx, long long ldw, const float* hconst,

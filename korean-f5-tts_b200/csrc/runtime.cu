@@ -316,6 +316,44 @@ int f5b_debug_attn_trace(int32_t rows, int32_t heads, int32_t batches, int64_t* 
   F5B_API_END
 }
 
+int f5b_debug_ktrace(int32_t op, int64_t capacity, int64_t* out, int64_t* n, int32_t device) {
+  F5B_API_BEGIN
+#if defined(F5B_KTRACE)
+  static unsigned long long* buf = nullptr;
+  static int64_t cap = 0;
+  open_device(device, F5B_MODE_BF16);
+  auto arm = [](unsigned long long* p) {
+    ktrace_set_tc_gemm(p);
+    ktrace_set_tc_attn(p);
+    ktrace_set_rowwise(p);
+  };
+  if (op == 0) {
+    F5B_REQUIRE(capacity > 0 && buf == nullptr, "trace already running or bad capacity");
+    F5B_CHECK_CUDA(cudaMalloc(&buf, (size_t)(4 + 8 * capacity) * 8));
+    F5B_CHECK_CUDA(cudaMemset(buf, 0, (size_t)(4 + 8 * capacity) * 8));
+    const unsigned long long c = (unsigned long long)capacity;
+    F5B_CHECK_CUDA(cudaMemcpy(buf + 1, &c, 8, cudaMemcpyHostToDevice));
+    cap = capacity;
+    arm(buf);
+  } else {
+    F5B_REQUIRE(buf != nullptr && out != nullptr && n != nullptr, "trace not running");
+    F5B_CHECK_CUDA(cudaDeviceSynchronize());
+    arm(nullptr);
+    unsigned long long cnt = 0;
+    F5B_CHECK_CUDA(cudaMemcpy(&cnt, buf, 8, cudaMemcpyDeviceToHost));
+    const int64_t take = std::min<int64_t>(std::min<int64_t>((int64_t)cnt, cap), *n);
+    F5B_CHECK_CUDA(cudaMemcpy(out, buf + 4, (size_t)take * 64, cudaMemcpyDeviceToHost));
+    *n = (int64_t)cnt;
+    cudaFree(buf);
+    buf = nullptr;
+  }
+#else
+  (void)op; (void)capacity; (void)out; (void)n; (void)device;
+  F5B_REQUIRE(false, "library built without F5B_KTRACE");
+#endif
+  F5B_API_END
+}
+
 int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, float* ms, int32_t device, void* stream) {
   F5B_API_BEGIN
   F5B_REQUIRE(ms != nullptr && iters > 0, "bad argument");

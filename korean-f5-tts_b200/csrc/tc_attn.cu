@@ -64,6 +64,8 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
   uint64_t* o_done = p_full + 2;                  // [2]  MMA -> softmax: the last PV_t has completed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 2);
 
+  KT_DECL
+  KT_BEGIN();
   pdl_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 2 * AT_BQ, h = blockIdx.y, b = blockIdx.z;
@@ -93,6 +95,7 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // qkv comes from the previous kernel; everything above overlapped its tail
+  KT_WAITED();
 
   if (warp == 8) {
     if (lane == 0) {
@@ -276,7 +279,10 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
     tc_fence_after();
     tmem_dealloc(tmem_base, AT_TMEM_COLS);
   }
+  KT_END(2);
 }
+
+KT_DEFINE_SETTER(ktrace_set_tc_attn)
 
 void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int rows, int heads, const int* kv_len,
                   float scale, int out_f16) {

@@ -9,8 +9,11 @@
 //   warp 0 lane 0 : TMA producer   -- cp.async.bulk.tensor into a STAGES-deep 128B-swizzled smem ring
 //   warp 1 lane 0 : MMA issuer     -- tcgen05.mma.cta_group::1.kind::f16, 128 x BN x 16 per instruction,
 //                                     fp32 accumulators in TMEM, double buffered (2 x BN columns)
-//   warps 2..5    : epilogue       -- tcgen05.ld 32x32b, fused bias / RoPE / activation / gate+residual,
-//                                     direct global stores; overlaps the next tile's MMAs
+//   warps 2..9    : epilogue       -- two groups of four warps (a warp reads the TMEM lane quarter warp%4); group g owns
+//                                     the 64-column units g, g+2, ... of the tile: tcgen05.ld 32x32b, fused bias / RoPE /
+//                                     activation / gate, swizzled smem staging, TMA store or L2 reduce-add; overlaps the
+//                                     next tile's MMAs.  Two warps per scheduler: the in-situ timeline showed the
+//                                     4-warp epilogue exposed for 5.5 us on the 1-tile-per-CTA shapes
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 #include "tc_gemm.h"
@@ -32,7 +35,8 @@ static constexpr int A_STAGE_BYTES = BM * BK * 2;
 // reduce-add (fp32, performed in L2) for the gate * y + residual update.  No per-thread global stores: every global
 // write is a full-line bulk transfer, and the residual is never read back by the SM.
 // ---------------------------------------------------------------------------------------------
-static constexpr int EPI_NBUF = 3;
+static constexpr int EPI_GROUPS = 2;  // epilogue warp groups
+static constexpr int EPI_NBUF = 2;    // staging buffers per group
 static constexpr int EPI_BUF_BYTES = BM * 128;  // 128 rows x 128 B (32 fp32 or 64 16-bit columns)
 
 // Activations of the tensor-core epilogue: single-MUFU forms (tanh.approx, ex2.approx, rcp.approx).  Their error
@@ -117,7 +121,7 @@ __device__ __forceinline__ void epi_transform(const EpiParams& p, float* v, int 
 }
 
 template <int BN, int STAGES>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(64 + 128 * EPI_GROUPS, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const TcGemmShape s, const EpiParams ep) {
   constexpr int B_STAGE_BYTES = BN * BK * 2;
@@ -129,7 +133,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_STAGE_BYTES;
   uint8_t* sO = smem + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
-  float* sBias = reinterpret_cast<float*>(sO + EPI_NBUF * EPI_BUF_BYTES);  // [BN] bias, [BN] gate of the current tile
+  float* sBias = reinterpret_cast<float*>(sO + EPI_GROUPS * EPI_NBUF * EPI_BUF_BYTES);  // [BN] bias, [BN] gate of the current tile
   float* sGate = sBias + BN;
   uint64_t* full = reinterpret_cast<uint64_t*>(sGate + BN);
   uint64_t* empty = full + STAGES;
@@ -137,6 +141,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
+  KT_DECL
+  KT_BEGIN();
   pdl_trigger();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -153,7 +159,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 4);
+      mbar_init(&tempty[i], 4 * EPI_GROUPS);
     }
     fence_barrier_init();
   }
@@ -180,6 +186,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
     pdl_wait();
+    KT_WAITED();
     for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x) {
       const int ks = unit % s.splits, tile = unit / s.splits;
       const int tm = tile / s.tiles_n, tn = tile - tm * s.tiles_n;
@@ -223,6 +230,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t st = it % STAGES, ph = (it / STAGES) & 1u;
       for (int kb = kb0; kb < kb1; ++kb, ++it) {
         mbar_wait(&full[st], ph);
+        if (it == 0) KT_MARK(2);  // first operands have landed
         tc_fence_after();
         const uint64_t ad = desc0 | (uint64_t)(a_lo + st * (A_STAGE_BYTES >> 4));
         const uint64_t bd = desc0 | (uint64_t)(b_lo + st * (B_STAGE_BYTES >> 4));
@@ -236,12 +244,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       umma_commit(&tfull[acc]);  // accumulator complete
+      KT_MARK(3);  // (last tile wins) all MMAs issued
     }
   } else if (warp >= 2) {
     // ------------------------------- epilogue -----------------------------------
     const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are this warp's
     const int rl = quarter * 32 + lane;  // row inside the tile
-    const bool issuer = threadIdx.x == 64;
+    const int grp = (warp - 2) >> 2;  // units of 64 columns alternate between the two groups
+    const bool issuer = ((warp - 2) & 3) == 0 && lane == 0;
+    uint8_t* sOg = sO + grp * EPI_NBUF * EPI_BUF_BYTES;
     const bool out32 = ep.kind == EPI_RESID || ep.out_type == OUT_F32;
     uint32_t tcount = 0, nstore = 0;
     for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x, ++tcount) {
@@ -264,12 +275,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       // stage this tile's bias / gate columns while its MMAs are still running
       for (int i = rl; i < BN; i += 128) {
+        if (((i >> 6) & 1) != grp) continue;  // each group stages (and later reads) only its own columns
         const int n = n0 + i;
         const bool in = n < ep.n_valid;
         sBias[i] = (ep.bias != nullptr && with_bias && in) ? __ldg(ep.bias + n) : 0.0f;
         sGate[i] = (ep.gate != nullptr && ep.gate_bmod <= 1 && in) ? __ldg(ep.gate + n) : 1.0f;
       }
-      named_bar_sync(1, 128);
+      named_bar_sync(1 + grp, 128);
       float4 rope_reg[16];
       const bool has_rope = ep.rope_cs != nullptr && n0 < ep.rope_cols;  // uniform per tile
       if (has_rope) {
@@ -281,10 +293,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 16; ++i) rope_reg[i] = make_float4(1.0f, 0.0f, 1.0f, 0.0f);
       }
       mbar_wait(&tfull[acc], aph);
+      if (issuer && grp == 0) KT_MARK(4);  // (last tile wins) accumulator complete, epilogue starts
       tc_fence_after();
       const uint32_t t_row = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll 1
-      for (int c = 0; c < BN; c += 32) {
+      for (int c = grp * 64; c < BN; c += (c & 32) ? 96 : 32) {
         const int n = n0 + c;
         if (n >= s.N) break;  // uniform: the rest of the tile lies beyond the last column
         float v[32];
@@ -297,7 +310,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           case ACT_SILU: epi_transform<ACT_SILU>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
           default: epi_transform<ACT_NONE>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
         }
-        uint8_t* buf = sO + (nstore % EPI_NBUF) * EPI_BUF_BYTES;
+        uint8_t* buf = sOg + (nstore % EPI_NBUF) * EPI_BUF_BYTES;
         uint8_t* row = buf + rl * 128;
         const int sw = rl & 7;
         bool flush;
@@ -333,12 +346,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (flush) {
           fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
-          named_bar_sync(1, 128);
+          // two staging buffers per group: the store issued at the previous flush has to be done reading its buffer
+          // before anyone passes this barrier and starts to fill it again (it had a whole chunk of time to do so)
+          if (issuer) bulk_wait_read<0>();
+          named_bar_sync(1 + grp, 128);
           if (issuer) {
             if (ep.kind == EPI_RESID) tma_reduce_add_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             else tma_store_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             bulk_commit();
-            bulk_wait_read<1>();  // the buffer written two stores from now is free again
           }
           ++nstore;
         }
@@ -347,7 +362,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
     }
-    if (issuer) bulk_wait<0>();
+    if (issuer && grp == 0) KT_MARK(5);  // last store issued
+    // the staging buffers must outlive the reads of the bulk stores; the writes themselves complete with the grid
+    if (issuer) bulk_wait_read<0>();
   }
 
   tc_fence_before();
@@ -356,7 +373,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc_fence_after();
     tmem_dealloc(tmem_base, ACC_COLS);
   }
+  KT_END(1);
 }
+
+KT_DEFINE_SETTER(ktrace_set_tc_gemm)
 
 // ---------------------------------------------------------------------------------------------
 // host side
@@ -409,12 +429,12 @@ void make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dim
 
 template <int BN, int STAGES>
 static constexpr int smem_bytes() {
-  return STAGES * (A_STAGE_BYTES + BN * BK * 2) + EPI_NBUF * EPI_BUF_BYTES + 2 * BN * 4 + 1024 + 256;
+  return STAGES * (A_STAGE_BYTES + BN * BK * 2) + EPI_GROUPS * EPI_NBUF * EPI_BUF_BYTES + 2 * BN * 4 + 1024 + 256;
 }
 template <int BN, int STAGES>
 static void launch_cfg(cudaStream_t st, int grid, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
                        const TcGemmShape& s, const EpiParams& ep) {
-  launch_pdl_id(1, tc_gemm_kernel<BN, STAGES>, dim3(grid), dim3(192), smem_bytes<BN, STAGES>(), st, ta, tb, to, s, ep);
+  launch_pdl_id(1, tc_gemm_kernel<BN, STAGES>, dim3(grid), dim3(64 + 128 * EPI_GROUPS), smem_bytes<BN, STAGES>(), st, ta, tb, to, s, ep);
   F5B_POST_LAUNCH();
 }
 
@@ -425,7 +445,7 @@ static void config_one() {
                                       smem_bytes<BN, STAGES>()));
 }
 void tc_gemm_init_kernels() {
-  config_one<64, 7>();
+  config_one<64, 6>();
   config_one<128, 5>();
   config_one<256, 3>();
 }
@@ -532,7 +552,7 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
   long long total = (long long)s.tiles_m_per_batch * batches * s.tiles_n * s.splits;
   int grid = (int)(total < sm_count ? total : sm_count);
   if (bn == 64)
-    launch_cfg<64, 7>(st, grid, ta, tb, to, s, ep);
+    launch_cfg<64, 6>(st, grid, ta, tb, to, s, ep);
   else if (bn == 128)
     launch_cfg<128, 5>(st, grid, ta, tb, to, s, ep);
   else

@@ -56,6 +56,9 @@ void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int 
 void simt_attention(cudaStream_t st, const float* qkv, float* out, int batches, int rows, int heads, const int* kv_len,
                     float scale);
 
+void ktrace_set_tc_gemm(unsigned long long* p);  // per-translation-unit trace pointers (no-ops without F5B_KTRACE)
+void ktrace_set_tc_attn(unsigned long long* p);
+void ktrace_set_rowwise(unsigned long long* p);
 void attn_trace_enable(int on);
 void attn_trace_read(long long* host /* [3][64][4] clock64 stamps */);
 void tc_init_kernels();       // attention

@@ -58,6 +58,7 @@ _SIGNATURES = {
     "f5b_op_time": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float), C.c_int32,
                               C.c_void_p]),
     "f5b_debug_attn_trace": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32]),
+    "f5b_debug_ktrace": (C.c_int, [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32]),
     "f5b_launch_count": (C.c_int64, []),
     "f5b_last_call_launches": (C.c_int64, []),
 }

@@ -35,6 +35,15 @@ static constexpr int A_STAGE_BYTES = BM * BK * 2;
 // reduce-add (fp32, performed in L2) for the gate * y + residual update.  No per-thread global stores: every global
 // write is a full-line bulk transfer, and the residual is never read back by the SM.
 // ---------------------------------------------------------------------------------------------
+// Epilogue variants.  The generic epilogue (any activation / output type / RoPE / gate, chosen at run time) is ~4600
+// SASS instructions per chunk iteration of which ~500 execute: ncu's source view showed the epilogue warps mostly
+// stalled on instruction fetch (no_inst) while hopping over the unused cases.  The three shapes of the per-step chain get
+// their own instantiation whose chunk loop holds only the code it runs; everything else uses the generic one.
+enum { EV_GENERIC = 0, EV_STORE16 = 1, EV_RESID = 2, EV_GELU16 = 3 };
+//   EV_STORE16: no activation, 16-bit store, optional RoPE, no gate          (qkv, plain projections)
+//   EV_RESID  : no activation, fp32 L2 reduce-add, optional per-column gate  (attention out-projection, ff2)
+//   EV_GELU16 : tanh-GELU, 16-bit store, no RoPE, no gate                    (ff1)
+
 static constexpr int EPI_GROUPS = 2;  // epilogue warp groups
 static constexpr int EPI_NBUF = 2;    // staging buffers per group
 static constexpr int EPI_BUF_BYTES = BM * 128;  // 128 rows x 128 B (32 fp32 or 64 16-bit columns)
@@ -79,7 +88,8 @@ __device__ __forceinline__ void rope_rotate(float* v, const float4 (&t)[16]) {
   }
 }
 
-template <int ACT>
+// ROPE: the variant can carry rotary columns; GATE: 0 = never, 1 = staged per-column gate only, 2 = staged or per-row.
+template <int ACT, bool ROPE, int GATE>
 __device__ __forceinline__ void epi_transform(const EpiParams& p, float* v, int n, int cs, int b, int pos, bool dead,
                                               const float* bias_s, const float* gate_s, const float4 (&rope)[16],
                                               bool has_rope) {
@@ -88,7 +98,7 @@ __device__ __forceinline__ void epi_transform(const EpiParams& p, float* v, int 
     const float4 bv = *reinterpret_cast<const float4*>(bias_s + cs + j);
     v[j] += bv.x; v[j + 1] += bv.y; v[j + 2] += bv.z; v[j + 3] += bv.w;
   }
-  if (has_rope && n < p.rope_cols) {
+  if (ROPE && has_rope && n < p.rope_cols) {
     const int within = n % p.rope_period;
     if ((within >> 6) < p.rope_heads) {
       // rope[0..16): this row's 32 (cos, sin) pairs, loaded once per tile; a 32-column chunk is half a head
@@ -100,8 +110,8 @@ __device__ __forceinline__ void epi_transform(const EpiParams& p, float* v, int 
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = act_fast<ACT>(v[j]);
   }
-  if (p.gate != nullptr) {
-    if (p.gate_bmod <= 1) {
+  if (GATE != 0 && p.gate != nullptr) {
+    if (GATE == 1 || p.gate_bmod <= 1) {
 #pragma unroll
       for (int j = 0; j < 32; j += 4) {
         const float4 gv = *reinterpret_cast<const float4*>(gate_s + cs + j);
@@ -120,7 +130,7 @@ __device__ __forceinline__ void epi_transform(const EpiParams& p, float* v, int 
   }
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int VAR>
 __global__ void __launch_bounds__(64 + 128 * EPI_GROUPS, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const TcGemmShape s, const EpiParams ep) {
@@ -253,7 +263,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int grp = (warp - 2) >> 2;  // units of 64 columns alternate between the two groups
     const bool issuer = ((warp - 2) & 3) == 0 && lane == 0;
     uint8_t* sOg = sO + grp * EPI_NBUF * EPI_BUF_BYTES;
-    const bool out32 = ep.kind == EPI_RESID || ep.out_type == OUT_F32;
+    constexpr bool GEN = VAR == EV_GENERIC;
+    constexpr bool MAY_ROPE = GEN || VAR == EV_STORE16;
+    const bool out32 = GEN ? (ep.kind == EPI_RESID || ep.out_type == OUT_F32) : (VAR == EV_RESID);
+    const bool resid = GEN ? ep.kind == EPI_RESID : (VAR == EV_RESID);
     uint32_t tcount = 0, nstore = 0;
     for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x, ++tcount) {
       const int ks = unit % s.splits, tile = unit / s.splits;
@@ -279,12 +292,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int n = n0 + i;
         const bool in = n < ep.n_valid;
         sBias[i] = (ep.bias != nullptr && with_bias && in) ? __ldg(ep.bias + n) : 0.0f;
-        sGate[i] = (ep.gate != nullptr && ep.gate_bmod <= 1 && in) ? __ldg(ep.gate + n) : 1.0f;
+        if (GEN || VAR == EV_RESID) sGate[i] = (ep.gate != nullptr && ep.gate_bmod <= 1 && in) ? __ldg(ep.gate + n) : 1.0f;
       }
       named_bar_sync(1 + grp, 128);
       float4 rope_reg[16];
-      const bool has_rope = ep.rope_cs != nullptr && n0 < ep.rope_cols;  // uniform per tile
-      if (has_rope) {
+      const bool has_rope = MAY_ROPE && ep.rope_cs != nullptr && n0 < ep.rope_cols;  // uniform per tile
+      if (!MAY_ROPE) {
+      } else if (has_rope) {
         const float4* src = reinterpret_cast<const float4*>(ep.rope_cs + (long long)pos * 64);
 #pragma unroll
         for (int i = 0; i < 16; ++i) rope_reg[i] = __ldg(src + i);
@@ -303,12 +317,20 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         float v[32];
         tmem_ld_32x32(t_row + c, v);
         tmem_ld_wait();
-        switch (ep.act) {
-          case ACT_GELU_TANH: epi_transform<ACT_GELU_TANH>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
-          case ACT_GELU_ERF: epi_transform<ACT_GELU_ERF>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
-          case ACT_MISH: epi_transform<ACT_MISH>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
-          case ACT_SILU: epi_transform<ACT_SILU>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
-          default: epi_transform<ACT_NONE>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+        if (GEN) {
+          switch (ep.act) {
+            case ACT_GELU_TANH: epi_transform<ACT_GELU_TANH, true, 2>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+            case ACT_GELU_ERF: epi_transform<ACT_GELU_ERF, true, 2>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+            case ACT_MISH: epi_transform<ACT_MISH, true, 2>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+            case ACT_SILU: epi_transform<ACT_SILU, true, 2>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+            default: epi_transform<ACT_NONE, true, 2>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope); break;
+          }
+        } else if (VAR == EV_STORE16) {
+          epi_transform<ACT_NONE, true, 0>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, has_rope);
+        } else if (VAR == EV_RESID) {
+          epi_transform<ACT_NONE, false, 1>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, false);
+        } else {
+          epi_transform<ACT_GELU_TANH, false, 0>(ep, v, n, c, b, pos, dead, sBias, sGate, rope_reg, false);
         }
         uint8_t* buf = sOg + (nstore % EPI_NBUF) * EPI_BUF_BYTES;
         uint8_t* row = buf + rl * 128;
@@ -351,7 +373,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (issuer) bulk_wait_read<0>();
           named_bar_sync(1 + grp, 128);
           if (issuer) {
-            if (ep.kind == EPI_RESID) tma_reduce_add_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
+            if (resid) tma_reduce_add_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             else tma_store_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             bulk_commit();
           }
@@ -431,18 +453,50 @@ template <int BN, int STAGES>
 static constexpr int smem_bytes() {
   return STAGES * (A_STAGE_BYTES + BN * BK * 2) + EPI_GROUPS * EPI_NBUF * EPI_BUF_BYTES + 2 * BN * 4 + 1024 + 256;
 }
+static int epilogue_variant(const EpiParams& ep) {
+  if (ep.kind == EPI_STORE && ep.out_type != OUT_F32 && ep.gate == nullptr) {
+    if (ep.act == ACT_NONE) return EV_STORE16;
+    if (ep.act == ACT_GELU_TANH && ep.rope_cs == nullptr) return EV_GELU16;
+  }
+  if (ep.kind == EPI_RESID && ep.act == ACT_NONE && ep.rope_cs == nullptr && (ep.gate == nullptr || ep.gate_bmod <= 1))
+    return EV_RESID;
+  return EV_GENERIC;
+}
+
+template <int BN, int STAGES, int VAR>
+static void launch_var(cudaStream_t st, int grid, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
+                       const TcGemmShape& s, const EpiParams& ep) {
+  launch_pdl_id(1, tc_gemm_kernel<BN, STAGES, VAR>, dim3(grid), dim3(64 + 128 * EPI_GROUPS), smem_bytes<BN, STAGES>(), st,
+                ta, tb, to, s, ep);
+  F5B_POST_LAUNCH();
+}
 template <int BN, int STAGES>
 static void launch_cfg(cudaStream_t st, int grid, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
                        const TcGemmShape& s, const EpiParams& ep) {
-  launch_pdl_id(1, tc_gemm_kernel<BN, STAGES>, dim3(grid), dim3(64 + 128 * EPI_GROUPS), smem_bytes<BN, STAGES>(), st, ta, tb, to, s, ep);
-  F5B_POST_LAUNCH();
+  if (BN >= 128) {  // the narrow tile only serves the conv / proj_out launches: generic epilogue
+    switch (epilogue_variant(ep)) {
+      case EV_STORE16: return launch_var<BN, STAGES, BN >= 128 ? EV_STORE16 : EV_GENERIC>(st, grid, ta, tb, to, s, ep);
+      case EV_RESID: return launch_var<BN, STAGES, BN >= 128 ? EV_RESID : EV_GENERIC>(st, grid, ta, tb, to, s, ep);
+      case EV_GELU16: return launch_var<BN, STAGES, BN >= 128 ? EV_GELU16 : EV_GENERIC>(st, grid, ta, tb, to, s, ep);
+      default: break;
+    }
+  }
+  launch_var<BN, STAGES, EV_GENERIC>(st, grid, ta, tb, to, s, ep);
 }
 
 template <int BN, int STAGES>
 static void config_one() {
   static_assert(smem_bytes<BN, STAGES>() <= 232448, "shared memory budget");
-  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, EV_GENERIC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       smem_bytes<BN, STAGES>()));
+  if (BN >= 128) {
+    F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, BN >= 128 ? EV_STORE16 : EV_GENERIC>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, STAGES>()));
+    F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, BN >= 128 ? EV_RESID : EV_GENERIC>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, STAGES>()));
+    F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, BN >= 128 ? EV_GELU16 : EV_GENERIC>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, STAGES>()));
+  }
 }
 void tc_gemm_init_kernels() {
   config_one<64, 6>();

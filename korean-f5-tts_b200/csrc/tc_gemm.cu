@@ -136,7 +136,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                const __grid_constant__ CUtensorMap tmO, const TcGemmShape s, const EpiParams ep) {
   constexpr int B_STAGE_BYTES = BN * BK * 2;
   constexpr uint32_t STAGE_TX = A_STAGE_BYTES + B_STAGE_BYTES;
-  constexpr uint32_t ACC_COLS = 2 * BN;
+  constexpr uint32_t ACC_COLS = 2 * BN <= 256 ? 2 * BN : 512;  // power of two; the two accumulators sit at 0 and BN
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -268,7 +268,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const bool out32 = GEN ? (ep.kind == EPI_RESID || ep.out_type == OUT_F32) : (VAR == EV_RESID);
     const bool resid = GEN ? ep.kind == EPI_RESID : (VAR == EV_RESID);
     uint32_t tcount = 0, nstore = 0;
-    for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x, ++tcount) {
+    // Dry pass: while the first tile's MMAs run, the epilogue warps walk one 64-column unit of the epilogue on whatever
+    // the accumulator holds -- no barrier wait, no bulk store -- so the code is in the instruction cache when the tile
+    // completes (the first chunk of a launch used to cost 2-3x a warm one, exposed on the one-tile-per-CTA shapes).
+    bool dry = true;
+    for (int unit = blockIdx.x; unit < total_tiles;) {
       const int ks = unit % s.splits, tile = unit / s.splits;
       const int tm = tile / s.tiles_n, tn = tile - tm * s.tiles_n;
       const int bz = tm / s.tiles_m_per_batch;
@@ -306,7 +310,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int i = 0; i < 16; ++i) rope_reg[i] = make_float4(1.0f, 0.0f, 1.0f, 0.0f);
       }
-      mbar_wait(&tfull[acc], aph);
+      if (!dry) mbar_wait(&tfull[acc], aph);
       if (issuer && grp == 0) KT_MARK(4);  // (last tile wins) accumulator complete, epilogue starts
       tc_fence_after();
       const uint32_t t_row = tmem_base + acc * BN + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -370,8 +374,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
           // two staging buffers per group: the store issued at the previous flush has to be done reading its buffer
           // before anyone passes this barrier and starts to fill it again (it had a whole chunk of time to do so)
-          if (issuer) bulk_wait_read<0>();
+          if (issuer && !dry) bulk_wait_read<0>();
           named_bar_sync(1 + grp, 128);
+          if (dry) break;
           if (issuer) {
             if (resid) tma_reduce_add_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             else tma_store_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
@@ -380,9 +385,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           ++nstore;
         }
       }
+      if (dry) {
+        dry = false;
+        continue;  // now the same unit for real
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
+      unit += gridDim.x;
+      ++tcount;
     }
     if (issuer && grp == 0) KT_MARK(5);  // last store issued
     // the staging buffers must outlive the reads of the bulk stores; the writes themselves complete with the grid
@@ -501,29 +512,31 @@ static void config_one() {
 void tc_gemm_init_kernels() {
   config_one<64, 6>();
   config_one<128, 5>();
+  config_one<192, 4>();
   config_one<256, 3>();
 }
 
-// Tile width and split-K factor.  Cost model from the measured sweep (tools/gemm_sweep.py, B200): one 64-deep k-block
-// costs ~0.26 / 0.30 / 0.37 us for 64 / 128 / 256-wide tiles (L2 operand traffic, not MMA issue, is the limit), a work
-// unit has ~1.5 us of fill + epilogue, and a CTA runs its units back to back.
+// Tile width and split-K factor.  Cost model from the in-situ timeline (tools/ktrace.py, B200): the MMA issuer needs
+// ~0.26 / 0.28 / 0.35 / 0.43 us per 64-deep k-block for 64 / 128 / 192 / 256-wide tiles (SS-mode operand reads, not the
+// tensor pipe, set the pace), a CTA runs its units back to back with the epilogue of all but the last hidden behind the
+// next unit's MMAs, and ~2 us of launch / pipeline fill / store drain do not depend on the tiling.
 static void pick_tiling(long long tiles_m, int N, int K, int sms, bool can_split, int force_bn, int force_splits,
                         int* bn_out, int* splits_out) {
-  const int cand[3] = {64, 128, 256};
-  const double kb_us[3] = {0.26, 0.30, 0.37};
+  const int cand[4] = {64, 128, 192, 256};
+  const double kb_us[4] = {0.26, 0.28, 0.35, 0.43};
+  const double epi_us[4] = {0.8, 1.4, 2.4, 2.5};
   const int num_kb = (K + BK - 1) / BK;
   double best_cost = 1e30;
   *bn_out = 128;
   *splits_out = 1;
-  for (int i = 0; i < 3; ++i) {
+  for (int i = 0; i < 4; ++i) {
     if (force_bn && cand[i] != force_bn) continue;
     for (int sp = 1; sp <= 4; sp *= 2) {
       if (force_splits && sp != force_splits) continue;
       if (sp > 1 && (!can_split || num_kb / sp < 4)) continue;
       long long units = tiles_m * ((N + cand[i] - 1) / cand[i]) * sp;
       long long rounds = (units + sms - 1) / sms;
-      double unit_us = kb_us[i] * ((num_kb + sp - 1) / sp) + 1.5 * cand[i] / 128.0;
-      double cost = rounds * unit_us;
+      double cost = rounds * (kb_us[i] * ((num_kb + sp - 1) / sp) + 0.15) + epi_us[i];
       if (cost < best_cost) {
         best_cost = cost;
         *bn_out = cand[i];
@@ -609,6 +622,8 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
     launch_cfg<64, 6>(st, grid, ta, tb, to, s, ep);
   else if (bn == 128)
     launch_cfg<128, 5>(st, grid, ta, tb, to, s, ep);
+  else if (bn == 192)
+    launch_cfg<192, 4>(st, grid, ta, tb, to, s, ep);
   else
     launch_cfg<256, 3>(st, grid, ta, tb, to, s, ep);
 }

@@ -48,7 +48,8 @@ def test_gemm_fp32(M, N, K, act):
 @pytest.mark.parametrize("M,N,K,act,bn", [(128, 128, 64, "none", 128), (256, 256, 256, "none", 64),
                                           (1880, 3072, 1024, "none", 0), (1880, 1024, 2048, "gelu_tanh", 256),
                                           (1880, 100, 1024, "none", 64), (940, 1024, 712, "none", 128),
-                                          (77, 520, 1000, "gelu", 0)])
+                                          (77, 520, 1000, "gelu", 0), (1880, 3072, 1024, "none", 192),
+                                          (300, 500, 320, "gelu_tanh", 192), (1880, 2048, 1024, "gelu_tanh", 128)])
 def test_gemm_bf16_tcgen05(M, N, K, act, bn):
     g = torch.Generator().manual_seed(M + N + K)
     a = torch.randn(M, K, generator=g)

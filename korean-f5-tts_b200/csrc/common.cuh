@@ -145,19 +145,31 @@ __device__ __forceinline__ unsigned long long ktrace_now() {
 #endif
 
 template <typename... P, typename... A>
-inline void launch_pdl_id(int kernel_id, void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
-                          A&&... args) {
+inline void launch_pdl_cluster(int kernel_id, int cluster_x, void (*kern)(P...), dim3 grid, dim3 block, size_t smem,
+                               cudaStream_t st, A&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[0].val.programmaticStreamSerializationAllowed = pdl_enabled(kernel_id) ? 1 : 0;
-  cfg.attrs = at;
   cfg.numAttrs = 1;
+  if (cluster_x > 1) {  // thread-block cluster along x (CTA pairs of the tcgen05 cta_group::2 kernels)
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = (unsigned)cluster_x;
+    at[1].val.clusterDim.y = 1;
+    at[1].val.clusterDim.z = 1;
+    cfg.numAttrs = 2;
+  }
+  cfg.attrs = at;
   F5B_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, P(args)...));
+}
+template <typename... P, typename... A>
+inline void launch_pdl_id(int kernel_id, void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                          A&&... args) {
+  launch_pdl_cluster(kernel_id, 1, kern, grid, block, smem, st, static_cast<A&&>(args)...);
 }
 
 __device__ __forceinline__ float act_apply(int act, float x) {

@@ -393,7 +393,7 @@ int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, f
     cudaGraphExecDestroy(ge);
     cudaGraphDestroy(g);
   };
-  if (which == 0 || which == 4 || which == 5 || which == 6 || which == 64 || which == 128 || which == 192 || which == 256) {
+  if (which == 0 || which == 4 || which == 5 || which == 6 || which == 64 || which == 128 || which == 192 || which == 256 || which > 1000) {
     // 0: bf16 store, tile width chosen by the library; 64/128/256: forced tile width; 4: gate*y + residual (fp32 reduce)
     long long ld = (K + 7) / 8 * 8;
     bf16* A = arena.alloc_n<bf16>((size_t)M * ld);

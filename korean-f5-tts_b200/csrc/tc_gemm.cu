@@ -130,12 +130,16 @@ __device__ __forceinline__ void epi_transform(const EpiParams& p, float* v, int 
   }
 }
 
-template <int BN, int STAGES, int VAR>
+template <int BN, int STAGES, int VAR, int PAIR>
 __global__ void __launch_bounds__(64 + 128 * EPI_GROUPS, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const TcGemmShape s, const EpiParams ep) {
-  constexpr int B_STAGE_BYTES = BN * BK * 2;
-  constexpr uint32_t STAGE_TX = A_STAGE_BYTES + B_STAGE_BYTES;
+  // PAIR: two CTAs (one TPC) share a 256-row tile -- each keeps its own 128 A rows and half of the B tile, so a CTA
+  // takes in A + B/2 per k-block instead of A + B: the mainloop is bound by the ~64 B/clk an SM can pull from L2
+  // (0.43 us per 48 KB k-block at BN = 256), not by the tensor pipe.
+  constexpr int BNL = PAIR ? BN / 2 : BN;  // B rows in this CTA's shared memory
+  constexpr int B_STAGE_BYTES = BNL * BK * 2;
+  constexpr uint32_t STAGE_TX = (A_STAGE_BYTES + B_STAGE_BYTES) * (PAIR ? 2 : 1);  // counted on the leader's barrier
   constexpr uint32_t ACC_COLS = 2 * BN <= 256 ? 2 * BN : 512;  // power of two; the two accumulators sit at 0 and BN
 
   extern __shared__ uint8_t smem_raw[];
@@ -156,8 +160,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   pdl_trigger();
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int tiles_m = s.tiles_m_per_batch * s.batches;
-  const int total_tiles = tiles_m * s.tiles_n * s.splits;  // work units: (tile, k-split)
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;  // 0 = leader: issues the MMAs, owns full[] and tempty[]
+  const int mrows = PAIR ? (s.tiles_m_per_batch + 1) / 2 : s.tiles_m_per_batch;  // tile rows (of BM * (1 + PAIR)) per batch
+  const int total_tiles = mrows * s.batches * s.tiles_n * s.splits;  // work units: (tile, k-split)
+  const int unit0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int unit_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
@@ -169,13 +176,17 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 4 * EPI_GROUPS);
+      mbar_init(&tempty[i], 4 * EPI_GROUPS * (PAIR ? 2 : 1));
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, ACC_COLS);
+  if (warp == 1) {
+    if (PAIR) tmem_alloc_pair(tmem_slot, ACC_COLS);
+    else tmem_alloc(tmem_slot, ACC_COLS);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything is signalled on them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -185,23 +196,25 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // programmatic-dependency wait, so their HBM latency overlaps the predecessor's tail; the A tiles follow after it.
     uint32_t it = 0;
     int pre = 0;
-    if (blockIdx.x < total_tiles) {
-      const int ks = blockIdx.x % s.splits, tile = blockIdx.x / s.splits;
+    const uint32_t full0 = PAIR ? cluster_map(&full[0], 0) : 0u;  // the leader's full[] barriers count both CTAs' bytes
+    if (unit0 < total_tiles) {
+      const int ks = unit0 % s.splits, tile = unit0 / s.splits;
       const int tn = tile % s.tiles_n;
       const int kb0 = ks * s.num_kb / s.splits, kb1 = (ks + 1) * s.num_kb / s.splits;
       pre = kb1 - kb0 < STAGES ? kb1 - kb0 : STAGES;
       for (int i = 0; i < pre; ++i) {
-        mbar_expect_tx(&full[i], STAGE_TX);
-        tma_load_2d(sB + i * B_STAGE_BYTES, &tmB, &full[i], (kb0 + i) * BK, tn * BN);
+        if (rank == 0) mbar_expect_tx(&full[i], STAGE_TX);
+        if (PAIR) tma_load_2d_pair(sB + i * B_STAGE_BYTES, &tmB, full0 + 8 * i, (kb0 + i) * BK, tn * BN + (int)rank * BNL);
+        else tma_load_2d(sB + i * B_STAGE_BYTES, &tmB, &full[i], (kb0 + i) * BK, tn * BN);
       }
     }
     pdl_wait();
     KT_WAITED();
-    for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x) {
+    for (int unit = unit0; unit < total_tiles; unit += unit_step) {
       const int ks = unit % s.splits, tile = unit / s.splits;
       const int tm = tile / s.tiles_n, tn = tile - tm * s.tiles_n;
-      const int bz = tm / s.tiles_m_per_batch;
-      const int r0 = (tm - bz * s.tiles_m_per_batch) * BM;
+      const int bz = tm / mrows;
+      const int r0 = ((tm - bz * mrows) * (PAIR ? 2 : 1) + (int)rank) * BM;  // beyond the batch for an odd tail: zero fill
       const int n0 = tn * BN;
       const int kb0 = ks * s.num_kb / s.splits, kb1 = (ks + 1) * s.num_kb / s.splits;
       for (int kb = kb0; kb < kb1; ++kb, ++it) {
@@ -209,7 +222,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool w_requested = (int)it < pre;  // first ring fill: W is already in flight, the slot is fresh
         if (!w_requested) {
           mbar_wait(&empty[st], ph ^ 1u);
-          mbar_expect_tx(&full[st], STAGE_TX);
+          if (rank == 0) mbar_expect_tx(&full[st], STAGE_TX);
         }
         int a_c0 = kb * BK, a_c1 = r0;
         if (s.conv) {
@@ -217,20 +230,25 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           a_c0 = (n0 / s.conv_cg) * s.conv_cg + sub * BK;
           a_c1 = r0 + tap - s.conv_pad;
         }
-        tma_load_3d(sA + st * A_STAGE_BYTES, &tmA, &full[st], a_c0, a_c1, bz);
-        if (!w_requested) tma_load_2d(sB + st * B_STAGE_BYTES, &tmB, &full[st], kb * BK, n0);
+        if (PAIR) {
+          tma_load_3d_pair(sA + st * A_STAGE_BYTES, &tmA, full0 + 8 * st, a_c0, a_c1, bz);
+          if (!w_requested) tma_load_2d_pair(sB + st * B_STAGE_BYTES, &tmB, full0 + 8 * st, kb * BK, n0 + (int)rank * BNL);
+        } else {
+          tma_load_3d(sA + st * A_STAGE_BYTES, &tmA, &full[st], a_c0, a_c1, bz);
+          if (!w_requested) tma_load_2d(sB + st * B_STAGE_BYTES, &tmB, &full[st], kb * BK, n0);
+        }
       }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1 && lane == 0 && rank == 0) {
     // ------------------------------- MMA issuer ---------------------------------
     // Descriptors are built once: only the 14-bit start-address field (bytes >> 4) changes between MMAs, and it cannot
     // carry out of its field (smem addresses < 256 KB), so a stage / k-step advance is a plain add.  The issuing thread
     // is a single lane: every instruction it spends per MMA is serial latency on the tensor pipe's critical path.
     const uint64_t desc0 = umma_desc_sw128(0, 16, 1024);
-    const uint32_t a_lo = smem_u32(sA) >> 4, b_lo = smem_u32(sB) >> 4;
+    const uint32_t a_lo = (smem_u32(sA) & 0x3FFFFu) >> 4, b_lo = (smem_u32(sB) & 0x3FFFFu) >> 4;
     const uint32_t idesc = s.idesc;
     uint32_t it = 0, tcount = 0;
-    for (int unit = blockIdx.x; unit < total_tiles; unit += gridDim.x, ++tcount) {
+    for (int unit = unit0; unit < total_tiles; unit += unit_step, ++tcount) {
       const int ks = unit % s.splits;
       const int kb0 = ks * s.num_kb / s.splits, kb1 = (ks + 1) * s.num_kb / s.splits;
       const uint32_t acc = tcount & 1u, aph = (tcount >> 1) & 1u;
@@ -244,16 +262,24 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc_fence_after();
         const uint64_t ad = desc0 | (uint64_t)(a_lo + st * (A_STAGE_BYTES >> 4));
         const uint64_t bd = desc0 | (uint64_t)(b_lo + st * (B_STAGE_BYTES >> 4));
-        umma_ss(d_tmem, ad, bd, idesc, kb != kb0 ? 1u : 0u);
+        if (PAIR) {
+          umma_ss_pair(d_tmem, ad, bd, idesc, kb != kb0 ? 1u : 0u);
 #pragma unroll
-        for (int k = 1; k < BK / 16; ++k) umma_ss(d_tmem, ad + 2 * k, bd + 2 * k, idesc, 1u);
-        umma_commit(&empty[st]);  // frees the smem slot once these MMAs have read it
+          for (int k = 1; k < BK / 16; ++k) umma_ss_pair(d_tmem, ad + 2 * k, bd + 2 * k, idesc, 1u);
+          umma_commit_pair(&empty[st]);  // frees the slot in both CTAs
+        } else {
+          umma_ss(d_tmem, ad, bd, idesc, kb != kb0 ? 1u : 0u);
+#pragma unroll
+          for (int k = 1; k < BK / 16; ++k) umma_ss(d_tmem, ad + 2 * k, bd + 2 * k, idesc, 1u);
+          umma_commit(&empty[st]);  // frees the smem slot once these MMAs have read it
+        }
         if (++st == STAGES) {
           st = 0;
           ph ^= 1u;
         }
       }
-      umma_commit(&tfull[acc]);  // accumulator complete
+      if (PAIR) umma_commit_pair(&tfull[acc]);  // accumulator complete (each CTA's epilogue waits on its own barrier)
+      else umma_commit(&tfull[acc]);
       KT_MARK(3);  // (last tile wins) all MMAs issued
     }
   } else if (warp >= 2) {
@@ -272,11 +298,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // the accumulator holds -- no barrier wait, no bulk store -- so the code is in the instruction cache when the tile
     // completes (the first chunk of a launch used to cost 2-3x a warm one, exposed on the one-tile-per-CTA shapes).
     bool dry = true;
-    for (int unit = blockIdx.x; unit < total_tiles;) {
+    const uint32_t tempty0 = PAIR ? cluster_map(&tempty[0], 0) : 0u;
+    for (int unit = unit0; unit < total_tiles;) {
       const int ks = unit % s.splits, tile = unit / s.splits;
       const int tm = tile / s.tiles_n, tn = tile - tm * s.tiles_n;
-      const int bz = tm / s.tiles_m_per_batch;
-      const int r0 = (tm - bz * s.tiles_m_per_batch) * BM;
+      const int bz = tm / mrows;
+      const int r0 = ((tm - bz * mrows) * (PAIR ? 2 : 1) + (int)rank) * BM;
       const int n0 = tn * BN;
       const uint32_t acc = tcount & 1u, aph = (tcount >> 1) & 1u;
       const bool with_bias = ks == 0;  // the bias joins exactly one of the partial sums
@@ -377,7 +404,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (issuer && !dry) bulk_wait_read<0>();
           named_bar_sync(1 + grp, 128);
           if (dry) break;
-          if (issuer) {
+          if (issuer && r0 < s.rows_per_batch) {
             if (resid) tma_reduce_add_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             else tma_store_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             bulk_commit();
@@ -391,8 +418,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
-      unit += gridDim.x;
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_cluster(tempty0 + 8 * acc);
+        else mbar_arrive(&tempty[acc]);
+      }
+      unit += unit_step;
       ++tcount;
     }
     if (issuer && grp == 0) KT_MARK(5);  // last store issued
@@ -401,10 +431,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();  // neither CTA may leave while its peer's MMAs / barrier arrivals still touch it
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, ACC_COLS);
+    if (PAIR) tmem_dealloc_pair(tmem_base, ACC_COLS);
+    else tmem_dealloc(tmem_base, ACC_COLS);
   }
   KT_END(1);
 }
@@ -460,9 +492,10 @@ void make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dim
   }
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int PAIR>
 static constexpr int smem_bytes() {
-  return STAGES * (A_STAGE_BYTES + BN * BK * 2) + EPI_GROUPS * EPI_NBUF * EPI_BUF_BYTES + 2 * BN * 4 + 1024 + 256;
+  return STAGES * (A_STAGE_BYTES + (PAIR ? BN / 2 : BN) * BK * 2) + EPI_GROUPS * EPI_NBUF * EPI_BUF_BYTES + 2 * BN * 4 +
+         1024 + 256;
 }
 static int epilogue_variant(const EpiParams& ep) {
   if (ep.kind == EPI_STORE && ep.out_type != OUT_F32 && ep.gate == nullptr) {
@@ -474,73 +507,83 @@ static int epilogue_variant(const EpiParams& ep) {
   return EV_GENERIC;
 }
 
-template <int BN, int STAGES, int VAR>
+template <int BN, int STAGES, int VAR, int PAIR>
 static void launch_var(cudaStream_t st, int grid, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
                        const TcGemmShape& s, const EpiParams& ep) {
-  launch_pdl_id(1, tc_gemm_kernel<BN, STAGES, VAR>, dim3(grid), dim3(64 + 128 * EPI_GROUPS), smem_bytes<BN, STAGES>(), st,
-                ta, tb, to, s, ep);
+  launch_pdl_cluster(1, PAIR ? 2 : 1, tc_gemm_kernel<BN, STAGES, VAR, PAIR>, dim3(grid), dim3(64 + 128 * EPI_GROUPS),
+                     smem_bytes<BN, STAGES, PAIR>(), st, ta, tb, to, s, ep);
   F5B_POST_LAUNCH();
 }
-template <int BN, int STAGES>
+template <int BN, int STAGES, int PAIR>
 static void launch_cfg(cudaStream_t st, int grid, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& to,
                        const TcGemmShape& s, const EpiParams& ep) {
-  if (BN >= 128) {  // the narrow tile only serves the conv / proj_out launches: generic epilogue
-    switch (epilogue_variant(ep)) {
-      case EV_STORE16: return launch_var<BN, STAGES, BN >= 128 ? EV_STORE16 : EV_GENERIC>(st, grid, ta, tb, to, s, ep);
-      case EV_RESID: return launch_var<BN, STAGES, BN >= 128 ? EV_RESID : EV_GENERIC>(st, grid, ta, tb, to, s, ep);
-      case EV_GELU16: return launch_var<BN, STAGES, BN >= 128 ? EV_GELU16 : EV_GENERIC>(st, grid, ta, tb, to, s, ep);
-      default: break;
-    }
+  constexpr bool SPECIAL = BN >= 128;  // the narrow tile only serves the conv / proj_out launches: generic epilogue
+  switch (epilogue_variant(ep)) {
+    case EV_STORE16: return launch_var<BN, STAGES, SPECIAL ? EV_STORE16 : EV_GENERIC, PAIR>(st, grid, ta, tb, to, s, ep);
+    case EV_RESID: return launch_var<BN, STAGES, SPECIAL ? EV_RESID : EV_GENERIC, PAIR>(st, grid, ta, tb, to, s, ep);
+    case EV_GELU16: return launch_var<BN, STAGES, SPECIAL ? EV_GELU16 : EV_GENERIC, PAIR>(st, grid, ta, tb, to, s, ep);
+    default: return launch_var<BN, STAGES, EV_GENERIC, PAIR>(st, grid, ta, tb, to, s, ep);
   }
-  launch_var<BN, STAGES, EV_GENERIC>(st, grid, ta, tb, to, s, ep);
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int PAIR>
 static void config_one() {
-  static_assert(smem_bytes<BN, STAGES>() <= 232448, "shared memory budget");
-  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, EV_GENERIC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      smem_bytes<BN, STAGES>()));
-  if (BN >= 128) {
-    F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, BN >= 128 ? EV_STORE16 : EV_GENERIC>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, STAGES>()));
-    F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, BN >= 128 ? EV_RESID : EV_GENERIC>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, STAGES>()));
-    F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, BN >= 128 ? EV_GELU16 : EV_GENERIC>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, STAGES>()));
-  }
+  constexpr bool SPECIAL = BN >= 128;
+  constexpr int bytes = smem_bytes<BN, STAGES, PAIR>();
+  static_assert(bytes <= 232448, "shared memory budget");
+  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, EV_GENERIC, PAIR>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, SPECIAL ? EV_STORE16 : EV_GENERIC, PAIR>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, SPECIAL ? EV_RESID : EV_GENERIC, PAIR>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  F5B_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel<BN, STAGES, SPECIAL ? EV_GELU16 : EV_GENERIC, PAIR>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
 }
 void tc_gemm_init_kernels() {
-  config_one<64, 6>();
-  config_one<128, 5>();
-  config_one<192, 4>();
-  config_one<256, 3>();
+  config_one<64, 6, 0>();
+  config_one<128, 5, 0>();
+  config_one<192, 4, 0>();
+  config_one<256, 3, 0>();
+  config_one<128, 6, 1>();
+  config_one<192, 5, 1>();
+  config_one<256, 4, 1>();
 }
 
-// Tile width and split-K factor.  Cost model from the in-situ timeline (tools/ktrace.py, B200): the MMA issuer needs
-// ~0.26 / 0.28 / 0.35 / 0.43 us per 64-deep k-block for 64 / 128 / 192 / 256-wide tiles (SS-mode operand reads, not the
-// tensor pipe, set the pace), a CTA runs its units back to back with the epilogue of all but the last hidden behind the
-// next unit's MMAs, and ~2 us of launch / pipeline fill / store drain do not depend on the tiling.
-static void pick_tiling(long long tiles_m, int N, int K, int sms, bool can_split, int force_bn, int force_splits,
-                        int* bn_out, int* splits_out) {
+// Tile width, CTA pairing and split-K factor.  Cost model from the in-situ timeline (tools/ktrace.py, B200): the mainloop
+// is paced by the bytes an SM takes in per 64-deep k-block (A 16 KB + B 128 B per tile column, ~64 B/clk): ~0.26 / 0.28 /
+// 0.35 / 0.43 us for 64 / 128 / 192 / 256-wide tiles; a CTA pair halves the B bytes per CTA (0.20 / 0.23 / 0.27 us, the
+// last one at the tensor pipe's own floor).  A CTA runs its units back to back with the epilogue of all but the last
+// hidden behind the next unit's MMAs; launch, pipeline fill and store drain do not depend on the tiling.
+static void pick_tiling(long long tiles_m_per_batch, int batches, int N, int K, int sms, bool can_split, bool can_pair,
+                        int force_bn, int force_pair, int force_splits, int* bn_out, int* pair_out, int* splits_out) {
   const int cand[4] = {64, 128, 192, 256};
-  const double kb_us[4] = {0.26, 0.28, 0.35, 0.43};
+  const double kb_us[2][4] = {{0.26, 0.28, 0.35, 0.43}, {9.9, 0.20, 0.23, 0.27}};
   const double epi_us[4] = {0.8, 1.4, 2.4, 2.5};
   const int num_kb = (K + BK - 1) / BK;
   double best_cost = 1e30;
   *bn_out = 128;
+  *pair_out = 0;
   *splits_out = 1;
-  for (int i = 0; i < 4; ++i) {
-    if (force_bn && cand[i] != force_bn) continue;
-    for (int sp = 1; sp <= 4; sp *= 2) {
-      if (force_splits && sp != force_splits) continue;
-      if (sp > 1 && (!can_split || num_kb / sp < 4)) continue;
-      long long units = tiles_m * ((N + cand[i] - 1) / cand[i]) * sp;
-      long long rounds = (units + sms - 1) / sms;
-      double cost = rounds * (kb_us[i] * ((num_kb + sp - 1) / sp) + 0.15) + epi_us[i];
-      if (cost < best_cost) {
-        best_cost = cost;
-        *bn_out = cand[i];
-        *splits_out = sp;
+  for (int pair = 0; pair <= 1; ++pair) {
+    if (pair && !can_pair) continue;
+    if (force_pair >= 0 && pair != force_pair) continue;
+    for (int i = pair ? 1 : 0; i < 4; ++i) {
+      if (force_bn && cand[i] != force_bn) continue;
+      for (int sp = 1; sp <= 4; sp *= 2) {
+        if (force_splits && sp != force_splits) continue;
+        if (sp > 1 && (pair || !can_split || num_kb / sp < 4)) continue;
+        const long long mrows = pair ? (tiles_m_per_batch + 1) / 2 : tiles_m_per_batch;
+        const long long units = mrows * batches * ((N + cand[i] - 1) / cand[i]) * sp;
+        const long long workers = pair ? sms / 2 : sms;
+        const long long rounds = (units + workers - 1) / workers;
+        const double cost = rounds * (kb_us[pair][i] * ((num_kb + sp - 1) / sp) + 0.15) + epi_us[i] + (pair ? 0.1 : 0.0);
+        if (cost < best_cost) {
+          best_cost = cost;
+          *bn_out = cand[i];
+          *pair_out = pair;
+          *splits_out = sp;
+        }
       }
     }
   }
@@ -556,6 +599,7 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
   s.tiles_m_per_batch = (rows_per_batch + BM - 1) / BM;
   s.N = N;
   int bn;
+  int pair = 0;  // CTA pairs (cta_group::2)
   int a_cols;  // width of the A matrix (TMA dim 0)
   if (conv != nullptr) {
     F5B_REQUIRE(conv->cg % BK == 0, "tensor-core conv needs channels-per-group % 64 == 0");
@@ -572,14 +616,17 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
     // (and flip 16-bit roundings downstream), so it is only used on request (F5B_SPLIT_K=1 / force_splits)
     static const bool allow_split = std::getenv("F5B_SPLIT_K") != nullptr;
     const bool can_split = ep.kind == EPI_RESID && ep.act == ACT_NONE && (allow_split || force_splits > 1);
-    pick_tiling((long long)s.tiles_m_per_batch * batches, N, K, sm_count, can_split, force_bn, force_splits, &bn,
-                &s.splits);
+    // force_bn: 0 = model's choice, 64..256 = that width on single CTAs, 1000 + width = that width on CTA pairs
+    static const bool no_pair = std::getenv("F5B_PAIR") == nullptr;  // measured slower than single CTAs so far: opt-in
+    const int fpair = force_bn >= 1000 ? 1 : force_bn > 0 ? 0 : -1;
+    pick_tiling(s.tiles_m_per_batch, batches, N, K, sm_count, can_split, !no_pair || fpair == 1, force_bn % 1000, fpair, force_splits,
+                &bn, &pair, &s.splits);
     a_cols = K;
   }
   s.tiles_n = (N + bn - 1) / bn;
   s.num_kb = (K + BK - 1) / BK;
   const int fp16 = fp16_operands || (conv != nullptr && conv->fp16);
-  s.idesc = fp16 ? umma_idesc_f16(BM, bn, 0, 0) : umma_idesc_bf16(BM, bn, 0, 0);
+  s.idesc = fp16 ? umma_idesc_f16(BM * (1 + pair), bn, 0, 0) : umma_idesc_bf16(BM * (1 + pair), bn, 0, 0);
 
   CUtensorMap ta, tb;
   {
@@ -591,7 +638,7 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
   {
     uint64_t dims[2] = {(uint64_t)K, (uint64_t)N};
     uint64_t strides[1] = {(uint64_t)ldw * 2};
-    uint32_t box[2] = {BK, (uint32_t)bn};
+    uint32_t box[2] = {BK, (uint32_t)(pair ? bn / 2 : bn)};
     make_tmap_bf16(&tb, W, 2, dims, strides, box, fp16);
   }
   // output map: 3-D like A so that tile rows beyond a batch element (and the rows dropped by row_skip, which land at
@@ -614,18 +661,26 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
     make_tmap(&to, base, 3, dims, strides, box, et);
   }
   if (sync_debug())
-    fprintf(stderr, "tc_gemm rows %d x %d N %d K %d bn %d splits %d conv %d kind %d out_type %d act %d row_skip %d\n",
-            rows_per_batch, batches, N, K, bn, s.splits, s.conv, ep.kind, ep.out_type, ep.act, ep.row_skip);
+    fprintf(stderr, "tc_gemm rows %d x %d N %d K %d bn %d pair %d splits %d conv %d kind %d out_type %d act %d row_skip %d\n",
+            rows_per_batch, batches, N, K, bn, pair, s.splits, s.conv, ep.kind, ep.out_type, ep.act, ep.row_skip);
+  if (pair) {
+    const long long units = (long long)((s.tiles_m_per_batch + 1) / 2) * batches * s.tiles_n;
+    const int pairs = (int)(units < sm_count / 2 ? units : sm_count / 2);
+    if (bn == 128) launch_cfg<128, 6, 1>(st, 2 * pairs, ta, tb, to, s, ep);
+    else if (bn == 192) launch_cfg<192, 5, 1>(st, 2 * pairs, ta, tb, to, s, ep);
+    else launch_cfg<256, 4, 1>(st, 2 * pairs, ta, tb, to, s, ep);
+    return;
+  }
   long long total = (long long)s.tiles_m_per_batch * batches * s.tiles_n * s.splits;
   int grid = (int)(total < sm_count ? total : sm_count);
   if (bn == 64)
-    launch_cfg<64, 6>(st, grid, ta, tb, to, s, ep);
+    launch_cfg<64, 6, 0>(st, grid, ta, tb, to, s, ep);
   else if (bn == 128)
-    launch_cfg<128, 5>(st, grid, ta, tb, to, s, ep);
+    launch_cfg<128, 5, 0>(st, grid, ta, tb, to, s, ep);
   else if (bn == 192)
-    launch_cfg<192, 4>(st, grid, ta, tb, to, s, ep);
+    launch_cfg<192, 4, 0>(st, grid, ta, tb, to, s, ep);
   else
-    launch_cfg<256, 3>(st, grid, ta, tb, to, s, ep);
+    launch_cfg<256, 3, 0>(st, grid, ta, tb, to, s, ep);
 }
 
 }  // namespace f5b

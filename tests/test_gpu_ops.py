@@ -49,7 +49,11 @@ def test_gemm_fp32(M, N, K, act):
                                           (1880, 3072, 1024, "none", 0), (1880, 1024, 2048, "gelu_tanh", 256),
                                           (1880, 100, 1024, "none", 64), (940, 1024, 712, "none", 128),
                                           (77, 520, 1000, "gelu", 0), (1880, 3072, 1024, "none", 192),
-                                          (300, 500, 320, "gelu_tanh", 192), (1880, 2048, 1024, "gelu_tanh", 128)])
+                                          (300, 500, 320, "gelu_tanh", 192), (1880, 2048, 1024, "gelu_tanh", 128),
+                                          # CTA pairs (cta_group::2): 1000 + tile width; odd row-tile counts leave half a pair empty
+                                          (256, 256, 128, "none", 1128), (1880, 3072, 1024, "none", 1192),
+                                          (1880, 2048, 1024, "gelu_tanh", 1256), (1880, 1024, 2048, "none", 1128),
+                                          (130, 200, 1000, "gelu", 1256), (940, 1024, 712, "silu", 1192)])
 def test_gemm_bf16_tcgen05(M, N, K, act, bn):
     g = torch.Generator().manual_seed(M + N + K)
     a = torch.randn(M, K, generator=g)

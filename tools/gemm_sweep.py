@@ -13,7 +13,7 @@ def t(which, M, N, K, iters=50):
 M = int(sys.argv[1]) if len(sys.argv) > 1 else 1880
 for name, n, k in [("qkv", 3072, 1024), ("attn_out", 1024, 1024), ("ff1", 2048, 1024), ("ff2", 1024, 2048), ("text_pw1", 1024, 512)]:
     row = []
-    for w in (0, 64, 128, 192, 256, 4, 5, 6):
+    for w in (0, 128, 192, 256, 1128, 1192, 1256, 4):
         ms = t(w, M, n, k)
         row.append(f"{w}: {ms*1e3:7.2f}us {2.0*M*n*k/ms/1e9:7.1f}TF")
     print(f"{name:9s} M={M} N={n} K={k} | " + " | ".join(row), flush=True)

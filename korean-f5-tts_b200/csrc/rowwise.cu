@@ -112,15 +112,19 @@ ln_mod_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int
 }
 
 // Register-resident variant for d <= 1024: the row is read from memory once (8 float4 per lane).
+// LN_REG_ROWS rows (one per warp) per CTA: 1880 rows -> 940 small CTAs spread evenly over the 148 SMs (8-row CTAs left
+// 87 SMs with two CTAs and 61 with one: the launch ran at the pace of the doubly loaded SMs).
+static constexpr int LN_REG_ROWS = 2;
+
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(32 * LN_REG_ROWS)
 ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d, const float* __restrict__ mul,
                   const float* __restrict__ add, float mul_off, long long vec_bstride, int rows_per_batch, int bmod,
                   float eps) {
   KT_DECL
   KT_BEGIN();
   pdl_trigger();
-  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const long long m = (long long)blockIdx.x * LN_REG_ROWS + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (m >= M) return;
   const float* xr = x + m * d;
@@ -180,7 +184,7 @@ void ln_mod(cudaStream_t st, const float* x, T* out, long long M, int d, const f
             float mul_off, long long vec_bstride, int rows_per_batch, int bmod, float eps) {
   F5B_REQUIRE(d % 4 == 0, "LayerNorm width must be a multiple of 4");
   if (d <= 1024)
-    launch_pdl_id(4, ln_mod_reg_kernel<T>, dim3(ceil_div_ll(M, 8)), dim3(256), 0, st, x, out, M, d, mul, add, mul_off,
+    launch_pdl_id(4, ln_mod_reg_kernel<T>, dim3(ceil_div_ll(M, LN_REG_ROWS)), dim3(32 * LN_REG_ROWS), 0, st, x, out, M, d, mul, add, mul_off,
                vec_bstride, rows_per_batch, bmod < 1 ? 1 : bmod, eps);
   else
     ln_mod_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride, rows_per_batch,
@@ -624,19 +628,30 @@ euler_xproj_kernel(const float* __restrict__ y, float* __restrict__ y_next, cons
     }
   }
   const int n = n0 + tx * 8;
-  if (n >= d) return;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const long long m = m0 + ty * 4 + i;
-    if (m >= M1) continue;
+  if (n < d) {
     for (int br = 0; br < branches; ++br) {
-      const long long o = (m + (long long)br * M1) * d + n;
-      const float4 h0 = *reinterpret_cast<const float4*>(hconst + o);
-      const float4 h1 = *reinterpret_cast<const float4*>(hconst + o + 4);
-      *reinterpret_cast<float4*>(hproj + o) =
-          make_float4(h0.x + acc[i][0], h0.y + acc[i][1], h0.z + acc[i][2], h0.w + acc[i][3]);
-      *reinterpret_cast<float4*>(hproj + o + 4) =
-          make_float4(h1.x + acc[i][4], h1.y + acc[i][5], h1.z + acc[i][6], h1.w + acc[i][7]);
+      // all eight loads of a branch in flight before the first store (this loop used to pay one L2 round trip per row)
+      float4 h[4][2];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const long long m = m0 + ty * 4 + i;
+        h[i][0] = h[i][1] = make_float4(0, 0, 0, 0);
+        if (m < M1) {
+          const long long o = (m + (long long)br * M1) * d + n;
+          h[i][0] = __ldg(reinterpret_cast<const float4*>(hconst + o));
+          h[i][1] = __ldg(reinterpret_cast<const float4*>(hconst + o + 4));
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const long long m = m0 + ty * 4 + i;
+        if (m >= M1) continue;
+        const long long o = (m + (long long)br * M1) * d + n;
+        *reinterpret_cast<float4*>(hproj + o) =
+            make_float4(h[i][0].x + acc[i][0], h[i][0].y + acc[i][1], h[i][0].z + acc[i][2], h[i][0].w + acc[i][3]);
+        *reinterpret_cast<float4*>(hproj + o + 4) =
+            make_float4(h[i][1].x + acc[i][4], h[i][1].y + acc[i][5], h[i][1].z + acc[i][6], h[i][1].w + acc[i][7]);
+      }
     }
   }
   KT_END(8);

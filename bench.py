@@ -143,12 +143,12 @@ def time_kernel(which: int, M: int, N: int, K: int, iters: int, stream) -> float
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of tc_gemm_kernel from the committed `ncu --set full`
-# capture of a C2 step (profiles/r1_ncu_full_tc_gemm_v4.txt, cold caches): ff1, ff2, qkv, attn_out.
-NCU_TRAFFIC_MB = {"ff1": 8.13, "ff2": 19.68, "qkv": 10.47, "attn_out": 13.73}
+# capture of a C2 step (profiles/r1_ncu_full_tc_gemm_v5.txt, cold caches): ff1, ff2, qkv, attn_out.
+NCU_TRAFFIC_MB = {"ff1": 8.08, "ff2": 19.63, "qkv": 10.42, "attn_out": 13.68}
 
 
 def roofline_gemm(stream, pk) -> dict:
-    """Dominant kernel = tc_gemm_kernel (tcgen05 GEMM, ~63 % of the step).  Every DiT block shape of one function
+    """Dominant kernel = tc_gemm_kernel (tcgen05 GEMM, ~59 % of the step).  Every DiT block shape of one function
     evaluation is timed live: `f5b_op_time` captures 20 launches into a CUDA graph, rotates the weight matrix over
     > 190 MB of copies so W streams from HBM exactly as in the sampling loop (activations stay L2-resident, as they do
     there), and times the graph with CUDA events on its stream.  achieved = sum(algorithmic flops) / sum(avg time);
@@ -174,7 +174,7 @@ def roofline_gemm(stream, pk) -> dict:
             "peak_source": pk["src"] + " MEASURED_PEAKS.json bf16_tflops (burst: kernel timed alone)",
             "unit": "TFLOP/s", "frac": round(ach / pk["tf"], 4),
             "traffic": round(sum(NCU_TRAFFIC_MB.values()) / 4 * 1e6), "traffic_note":
-            "mean dram read+write bytes per launch over the 4 shapes (ncu --set full, profiles/r1_ncu_full_tc_gemm_v4.txt)",
+            "mean dram read+write bytes per launch over the 4 shapes (ncu --set full, profiles/r1_ncu_full_tc_gemm_v5.txt)",
             "per_shape": per,
             "other_kernels": {
                 "tc_attn_kernel": {"us": round(att_ms * 1e3, 2), "tflops": round(att_f / att_ms / 1e9, 1),

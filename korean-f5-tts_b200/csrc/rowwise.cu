@@ -112,9 +112,8 @@ ln_mod_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int
 }
 
 // Register-resident variant for d <= 1024: the row is read from memory once (8 float4 per lane).
-// LN_REG_ROWS rows (one per warp) per CTA: 1880 rows -> 940 small CTAs spread evenly over the 148 SMs (8-row CTAs left
-// 87 SMs with two CTAs and 61 with one: the launch ran at the pace of the doubly loaded SMs).
-static constexpr int LN_REG_ROWS = 2;
+// LN_REG_ROWS rows (one per warp) per CTA (2-row CTAs, 940 of them at C2, measured the same step time as 8-row ones).
+static constexpr int LN_REG_ROWS = 8;
 
 template <typename T>
 __global__ void __launch_bounds__(32 * LN_REG_ROWS)
@@ -516,7 +515,7 @@ euler_xproj_kernel(const float* __restrict__ y, float* __restrict__ y_next, cons
                    const float* __restrict__ hconst, float* __restrict__ hproj, int d) {
   extern __shared__ float xp_smem[];
   float* ws = xp_smem;                // [mel][XP_BN]
-  float* xs = xp_smem + mel * XP_BN;  // [XP_BM][mel + 1]
+  float* xs = xp_smem + mel * XP_BN;  // [XP_BM][mel + 4]: rows stay 16-byte aligned for float4 reads
   KT_DECL
   KT_BEGIN();
   pdl_trigger();
@@ -524,7 +523,7 @@ euler_xproj_kernel(const float* __restrict__ y, float* __restrict__ y_next, cons
   const int n0 = blockIdx.x * XP_BN;
   const long long m0 = (long long)blockIdx.y * XP_BM;
   const long long M1 = (long long)B * rows;
-  const int xld = mel + 1;
+  const int xld = mel + 4;
   // weights first: they do not depend on the previous kernel.  All loads of a batch are issued before the first use
   // (the in-situ timeline showed both loops of this kernel paying one L2 round trip per iteration: 20 + 20 us).
   if (hproj != nullptr) {
@@ -603,30 +602,38 @@ euler_xproj_kernel(const float* __restrict__ y, float* __restrict__ y_next, cons
           }
           if (writer && traj) *reinterpret_cast<float4*>(traj + off[u]) = o;
         }
-        float* xr = xs + r * xld + c;
-        xr[0] = o.x; xr[1] = o.y; xr[2] = o.z; xr[3] = o.w;
+        *reinterpret_cast<float4*>(xs + r * xld + c) = o;
       }
     }
   }
   if (hproj == nullptr) return;
   __syncthreads();
+  if (tid == 0) KT_MARK(2);  // row tile staged
   const int tx = tid & 15, ty = tid >> 4;
   float acc[4][8];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[i][j] = 0.0f;
-  for (int k = 0; k < mel; ++k) {
-    const float4 w0 = *reinterpret_cast<const float4*>(ws + k * XP_BN + tx * 8);
-    const float4 w1 = *reinterpret_cast<const float4*>(ws + k * XP_BN + tx * 8 + 4);
-    const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+  // four k per step: one float4 of each of the thread's 4 rows, eight float4 of weights, 128 FMAs
+  for (int k = 0; k < mel; k += 4) {
+    float4 a4[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float a = xs[(ty * 4 + i) * xld + k];
+    for (int i = 0; i < 4; ++i) a4[i] = *reinterpret_cast<const float4*>(xs + (ty * 4 + i) * xld + k);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a, wv[j], acc[i][j]);
+    for (int kk = 0; kk < 4; ++kk) {
+      const float4 w0 = *reinterpret_cast<const float4*>(ws + (k + kk) * XP_BN + tx * 8);
+      const float4 w1 = *reinterpret_cast<const float4*>(ws + (k + kk) * XP_BN + tx * 8 + 4);
+      const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float a = kk == 0 ? a4[i].x : kk == 1 ? a4[i].y : kk == 2 ? a4[i].z : a4[i].w;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a, wv[j], acc[i][j]);
+      }
     }
   }
+  if (tid == 0) KT_MARK(3);  // contraction done
   const int n = n0 + tx * 8;
   if (n < d) {
     for (int br = 0; br < branches; ++br) {
@@ -663,7 +670,7 @@ void euler_xproj(cudaStream_t st, const float* y, float* y_next, const float* v,
                  float dt, float cfg, float* traj_slot, const float* Wx, long long ldw, const float* hconst,
                  float* hproj, int d) {
   F5B_REQUIRE(mel % 4 == 0 && d % 8 == 0 && ldw % 4 == 0, "euler_xproj needs mel % 4 == 0, dim % 8 == 0");
-  const size_t smem = (size_t)(mel * XP_BN + XP_BM * (mel + 1)) * sizeof(float);
+  const size_t smem = (size_t)(mel * XP_BN + XP_BM * (mel + 4)) * sizeof(float);
   static size_t configured = 0;
   if (smem > configured) {
     F5B_CHECK_CUDA(cudaFuncSetAttribute(euler_xproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

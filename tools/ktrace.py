@@ -71,7 +71,9 @@ def main():
                          # GEMM phases, median over CTAs: operands landed, MMAs issued, accumulator complete, stores issued
                          ph=[float(np.median(a[:, 4] - a[:, 1])) / 1e3, float(np.median(a[:, 5] - a[:, 4])) / 1e3,
                              float(np.median(a[:, 6] - a[:, 5])) / 1e3, float(np.median(a[:, 7] - a[:, 6])) / 1e3,
-                             float(np.median(a[:, 2] - a[:, 7])) / 1e3] if kid == 1 else None))
+                             float(np.median(a[:, 2] - a[:, 7])) / 1e3] if kid == 1 else
+                         [float(np.median(a[:, 4] - a[:, 1])) / 1e3, float(np.median(a[:, 5] - a[:, 4])) / 1e3,
+                          float(np.median(a[:, 2] - a[:, 5])) / 1e3] if kid == 8 else None))
         prev_end = le
     eul = [i for i, r in enumerate(rows) if r["kid"] == 8]
     print(f"{len(rows)} launches, {len(eul)} euler_xproj")
@@ -80,7 +82,8 @@ def main():
     print(f"\none evaluation (launches {a}..{b}): {span:.1f} us wall")
     print(f"{'kernel':12s} {'ctas':>5s} {'gap':>6s} {'ramp':>6s} {'busy':>7s} {'tail':>6s} {'pre-wait':>8s}")
     for r in rows[a : a + 16] + rows[b - 4 : b + 1]:
-        ph = "" if r["ph"] is None else "   fill %.2f  issue %.2f  drain %.2f  epilogue %.2f  store %.2f" % tuple(r["ph"])
+        ph = "" if r["ph"] is None else ("   fill %.2f  issue %.2f  drain %.2f  epilogue %.2f  store %.2f" % tuple(r["ph"])
+                                          if len(r["ph"]) == 5 else "   stage %.2f  contract %.2f  add+store %.2f" % tuple(r["ph"]))
         print(f"{NAMES.get(r['kid'], r['kid']):12s} {r['ctas']:5d} {r['gap']:6.2f} {r['ramp']:6.2f} {r['busy']:7.2f} "
               f"{r['tail']:6.2f} {r['entry_lead']:8.2f}{ph}")
     agg = {}

@@ -88,6 +88,15 @@ int f5b_forward(f5b_plan* plan, const float* x, const float* cond, const int64_t
                 int32_t cfg_infer, int32_t cache, float* out, int32_t mem, void* stream);
 int f5b_clear_cache(f5b_plan* plan);
 
+/* Replaces the forward half of CFM.forward (model/cfm.py:231-302), i.e. the flow-matching loss of one training batch
+ * after the random draws (which stay host-side Python like the reference's): phi = (1 - t) x0 + t x1, cond = x1 outside
+ * the random span, one backbone evaluation with the drop flags, MSE against x1 - x0 over the span frames.
+ *   x1, x0 [B, N, mel]; time [B] HOST floats; lens [B] int32 or NULL; span [B, N] uint8 = rand_span_mask & lens mask.
+ * Outputs: loss [1]; cond, pred [B, N, mel] (either may be NULL).  No gradients: the backward pass is not built. */
+int f5b_cfm_loss(f5b_plan* plan, const float* x1, const float* x0, const int64_t* text, const float* time,
+                 const int32_t* lens, const uint8_t* span, int32_t B, int32_t N, int32_t nt, int32_t drop_audio_cond,
+                 int32_t drop_text, float* loss, float* cond, float* pred, int32_t mem, void* stream);
+
 /* Replaces MelSpec.forward (model/modules.py:78-104,133-146): wav [B, nw] -> mel [B, 100, nw/256 + 1]. */
 int f5b_mel(const float* wav, int32_t B, int32_t nw, float* mel, int32_t device, int32_t mem, void* stream);
 

@@ -501,6 +501,86 @@ void cfg_euler(cudaStream_t st, float* y, const float* v, int v_lead_rows, float
 }
 
 // ---------------------------------------------------------------------------------------------
+// Flow-matching loss, forward half (cfm.py:264-300)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+cfm_mix_kernel(const float* __restrict__ x1, const float* __restrict__ x0, const float* __restrict__ t,
+               const unsigned char* __restrict__ span, int rows, int mel, long long total, float* __restrict__ phi,
+               float* __restrict__ cond) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  const long long m = i / mel;
+  const float tb = t[m / rows];
+  const float a = x1[i], z = x0[i];
+  phi[i] = (1.0f - tb) * z + tb * a;
+  cond[i] = span[m] ? 0.0f : a;
+}
+
+void cfm_mix(cudaStream_t st, const float* x1, const float* x0, const float* t_dev, const unsigned char* span, int B,
+             int rows, int mel, float* phi, float* cond) {
+  const long long total = (long long)B * rows * mel;
+  cfm_mix_kernel<<<(unsigned)ceil_div_ll(total, 256), 256, 0, st>>>(x1, x0, t_dev, span, rows, mel, total, phi, cond);
+  F5B_POST_LAUNCH();
+}
+
+static constexpr int MSE_BLOCKS = 256;
+
+// block b sums the span rows b, b + 256, ...: per-thread partial -> warp shuffle tree -> 8 warp sums added in order
+__global__ void __launch_bounds__(256)
+masked_mse_partial_kernel(const float* __restrict__ pred, const float* __restrict__ x1, const float* __restrict__ x0,
+                          const unsigned char* __restrict__ span, long long rows_total, int mel,
+                          double* __restrict__ partials) {
+  __shared__ double ws[8];
+  __shared__ double wc[8];
+  double acc = 0.0, cnt = 0.0;
+  for (long long m = blockIdx.x; m < rows_total; m += MSE_BLOCKS) {
+    if (!span[m]) continue;
+    for (int c = threadIdx.x; c < mel; c += 256) {
+      const long long i = m * mel + c;
+      const float d = pred[i] - (x1[i] - x0[i]);
+      acc += (double)(d * d);
+      cnt += 1.0;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    ws[threadIdx.x >> 5] = acc;
+    wc[threadIdx.x >> 5] = cnt;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0.0, c = 0.0;
+    for (int w = 0; w < 8; ++w) {
+      a += ws[w];
+      c += wc[w];
+    }
+    partials[blockIdx.x] = a;
+    partials[MSE_BLOCKS + blockIdx.x] = c;
+  }
+}
+
+__global__ void masked_mse_final_kernel(const double* __restrict__ partials, float* __restrict__ loss) {
+  double a = 0.0, c = 0.0;
+  for (int b = 0; b < MSE_BLOCKS; ++b) {
+    a += partials[b];
+    c += partials[MSE_BLOCKS + b];
+  }
+  *loss = (float)(a / c);  // no span frame at all: 0 / 0 = NaN, like the mean of an empty selection in the reference
+}
+
+void masked_mse(cudaStream_t st, const float* pred, const float* x1, const float* x0, const unsigned char* span,
+                long long rows_total, int mel, double* partials, float* loss) {
+  masked_mse_partial_kernel<<<MSE_BLOCKS, 256, 0, st>>>(pred, x1, x0, span, rows_total, mel, partials);
+  F5B_POST_LAUNCH();
+  masked_mse_final_kernel<<<1, 1, 0, st>>>(partials, loss);
+  F5B_POST_LAUNCH();
+}
+
+// ---------------------------------------------------------------------------------------------
 // Fused CFG combine + Euler update + x-half of the input projection (cfm.py:162-191, torchdiffeq Euler, dit.py:138):
 //   y <- y + dt * (v_c + (v_c - v_u) * cfg)            (fp32; v == null: y unchanged -- the first evaluation)
 //   h[br] = hconst[br] + y W_x^T   for both CFG branches (the x columns are identical for cond / uncond, so the

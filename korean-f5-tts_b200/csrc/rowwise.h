@@ -49,6 +49,12 @@ void cfg_euler(cudaStream_t st, float* y, const float* v, int v_lead_rows, float
 // out = masked cast of x; copy (optional) = x unchanged (seeds the residual stream for the conv pos-emb epilogue)
 // Fused CFG + Euler update of y and x-half of the input projection: hproj[br] = hconst[br] + y W_x^T (null hproj: update
 // only).  The new state goes to y_next (column tiles of a row tile run in different CTAs).  v == null leaves y unchanged (first evaluation / f5b_forward).
+// Flow-matching training target (cfm.py:271-282): phi = (1 - t_b) x0 + t_b x1, cond = span ? 0 : x1.
+void cfm_mix(cudaStream_t st, const float* x1, const float* x0, const float* t_dev, const unsigned char* span, int B,
+             int rows, int mel, float* phi, float* cond);
+// mean over the span frames of (pred - (x1 - x0))^2 (cfm.py:298-300); fixed reduction order.  partials: [2 * 256] doubles.
+void masked_mse(cudaStream_t st, const float* pred, const float* x1, const float* x0, const unsigned char* span,
+                long long rows_total, int mel, double* partials, float* loss);
 void euler_xproj(cudaStream_t st, const float* y, float* y_next, const float* v, int v_lead_rows, int B, int branches, int rows, int mel,
                  float dt, float cfg, float* traj_slot, const float* Wx, long long ldw, const float* hconst,
                  float* hproj, int d);

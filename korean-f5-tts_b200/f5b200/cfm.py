@@ -3,10 +3,11 @@
 Host side (PyTorch, must match the reference exactly): mel of a raw-wave prompt, lens / duration / mask
 construction, token lookup, seeded noise, EPSS + sway time grid, the final `where(cond_mask, cond, out)`.
 Device side (libf5b200, one call): text embedding cache, every CFG-doubled backbone evaluation, Euler updates.
-`forward` (training loss, cfm.py:231-302) is outside the hot path and not provided.
+`forward` (cfm.py:231-302) evaluates the flow-matching loss through one C-ABI call; it produces no gradients.
 """
 from __future__ import annotations
 
+from random import random
 from typing import Callable
 
 import torch
@@ -42,8 +43,62 @@ class CFM(nn.Module):
     def device(self):
         return next(self.parameters()).device
 
-    def forward(self, *a, **k):
-        raise NotImplementedError("CFM.forward (training loss) is outside the B200 hot path; see DESIGN.md")
+    def forward(self, inp, text, *, lens=None, noise_scheduler=None, draws: dict | None = None):
+        """Flow-matching loss of one batch (cfm.py:231-302) -> (loss, cond, pred).
+
+        The random quantities are drawn on the host side in the reference's order and on the reference's devices
+        (`frac_lengths`, the span start, `x0`, `time` on `self.device`; the two drop decisions from `random()`), the rest
+        -- phi, the infilling condition, the backbone evaluation, the masked MSE -- is one `f5b_cfm_loss` call.
+        `draws` (keys frac_lengths, rand, x0, time, drop_audio_cond, drop_text) injects them instead (parity tests).
+        Forward only: the result carries no autograd graph (the backward kernels are not built)."""
+        if inp.ndim == 2:  # raw wave (cfm.py:240-243)
+            inp = self.mel_spec(inp).permute(0, 2, 1)
+            assert inp.shape[-1] == self.num_channels
+        dev = self.device
+        inp = inp.to(dev, torch.float32)
+        batch, seq_len = inp.shape[:2]
+        if isinstance(text, list):  # cfm.py:248-253
+            text = (list_str_to_idx(text, self.vocab_char_map) if exists(self.vocab_char_map)
+                    else list_str_to_tensor(text)).to(dev)
+            assert text.shape[0] == batch
+        if not exists(lens):
+            lens = torch.full((batch,), seq_len, device=dev)
+        lens = lens.to(dev)
+        mask = lens_to_mask(lens, length=seq_len)
+        if draws is None:
+            frac_lengths = torch.zeros((batch,), device=dev).float().uniform_(*self.frac_lengths_mask)
+            rand = torch.rand_like(frac_lengths)
+            x0 = torch.randn_like(inp)
+            time = torch.rand((batch,), dtype=inp.dtype, device=dev)
+            drop_audio_cond = random() < self.audio_drop_prob
+            if random() < self.cond_drop_prob:
+                drop_audio_cond, drop_text = True, True
+            else:
+                drop_text = False
+        else:
+            frac_lengths, rand = draws["frac_lengths"].to(dev), draws["rand"].to(dev)
+            x0, time = draws["x0"].to(dev, torch.float32), draws["time"].to(dev, torch.float32)
+            drop_audio_cond, drop_text = bool(draws["drop_audio_cond"]), bool(draws["drop_text"])
+        # random span to infill (model/utils.py:61-77), clipped to the utterance lengths
+        span_len = (frac_lengths * lens).long()
+        start = ((lens - span_len) * rand).long().clamp(min=0)
+        seq = torch.arange(seq_len, device=dev)
+        span = (seq[None, :] >= start[:, None]) & (seq[None, :] < (start + span_len)[:, None]) & mask
+
+        x1 = inp.contiguous()
+        x0 = x0.contiguous()
+        tx = text.to(device=dev, dtype=torch.long).contiguous()
+        ln = lens.to(torch.int32).contiguous()
+        sp = span.to(torch.uint8).contiguous()
+        t_host = time.detach().to("cpu", torch.float32).contiguous()
+        loss = torch.empty((1,), device=dev, dtype=torch.float32)
+        cond = torch.empty_like(x1)
+        pred = torch.empty_like(x1)
+        _lib.check(_lib.lib().f5b_cfm_loss(
+            self.transformer.plan(), x1.data_ptr(), x0.data_ptr(), tx.data_ptr(), t_host.data_ptr(), ln.data_ptr(),
+            sp.data_ptr(), batch, seq_len, tx.shape[1], int(drop_audio_cond), int(drop_text), loss.data_ptr(),
+            cond.data_ptr(), pred.data_ptr(), _lib.mem_kind(x1), _lib.current_stream_ptr(dev)))
+        return loss[0], cond, pred
 
     def prepare_inputs(self, cond, text, duration, *, lens=None, steps=32, sway_sampling_coef=None, seed=None,
                        max_duration=65536, use_epss=True, no_ref_audio=False, duplicate_test=False, t_inter=0.1,

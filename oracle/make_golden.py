@@ -65,6 +65,20 @@ def main():
         np.savez_compressed(os.path.join(out_dir, name + ".npz"), out=out.numpy(), traj_first=traj[1].numpy(),
                             traj_mid=traj[steps // 2].numpy(), weight_abs_sum=np.float64(wsum))
         print(name, tuple(out.shape), "weights |sum|", wsum)
+    # flow-matching loss (CFM.forward, cfm.py:231-302): the reference run under seeded CPU generators
+    import random
+    for name, seed in (("dit_v1style_b3_mask", 21), ("unett_b1", 22), ("dit_smallstyle_b2_nomask", 23)):
+        cfg, cond, text, lens, durs, *_ = case_inputs(name)
+        sd = O.synth_backbone_weights(cfg, seed=11)
+        cfm = build_reference(R, cfg, sd)
+        x1 = cond[:, : int(lens.max())]  # the "training mel" batch: the prompt frames, ragged by lens
+        torch.manual_seed(seed)
+        random.seed(seed)
+        with torch.no_grad():
+            loss, c, pred = cfm(x1, text, lens=lens)
+        np.savez_compressed(os.path.join(out_dir, "loss_" + name + ".npz"), loss=loss.numpy(), cond=c.numpy(),
+                            pred=pred.numpy(), seed=np.int64(seed))
+        print("loss", name, float(loss))
     # mel frontend: reference MelSpec on a seeded waveform
     g = torch.Generator().manual_seed(3)
     wav = torch.randn(2, 24000, generator=g) * 0.1

@@ -79,8 +79,9 @@ def test_unsupported_options_raise():
         f5b200.MelSpec(mel_spec_type="bigvgan")
     with pytest.raises(ValueError):
         f5b200.CFM(transformer=f5b200.DiT(dim=128, depth=1, heads=2), odeint_kwargs=dict(method="midpoint"))
-    with pytest.raises(NotImplementedError):
-        f5b200.CFM(transformer=f5b200.DiT(dim=128, depth=1, heads=2))(torch.zeros(1, 4, 100), ["a"])
+    if not torch.cuda.is_available():  # the loss path has no CPU fallback either: it must fail loudly, not fall back
+        with pytest.raises(RuntimeError):
+            f5b200.CFM(transformer=f5b200.DiT(dim=128, depth=1, heads=2))(torch.zeros(1, 4, 100), torch.zeros(1, 2).long())
 
 
 def test_precision_switches_keep_fp32_masters():

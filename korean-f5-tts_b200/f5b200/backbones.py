@@ -116,8 +116,22 @@ class _PlanBackbone(nn.Module):
         raise NotImplementedError
 
     def _signature(self):
-        ps = list(self.parameters())
+        # Walking the module tree costs ~1 ms of Python per call (363 parameters); the list of Parameter objects is kept
+        # and dropped whenever nn.Module._apply runs (.to / .cuda / .float ...).  In-place updates (load_state_dict,
+        # copy_, optimizer steps) keep the objects and bump `_version`, which the signature still sees.
+        ps = getattr(self, "_ps", None)
+        if ps is None:
+            ps = self._ps = list(self.parameters())
         return (str(ps[0].device), self.precision, tuple(p._version for p in ps), tuple(p.data_ptr() for p in ps))
+
+    def _apply(self, fn, *args, **kwargs):
+        self._ps = None
+        return super()._apply(fn, *args, **kwargs)
+
+    def invalidate_plan(self):
+        """Call after replacing a Parameter object of a sub-module (in-place updates are detected automatically)."""
+        self._ps = None
+        self._drop_plan()
 
     def _drop_plan(self):
         if getattr(self, "_plan", None):

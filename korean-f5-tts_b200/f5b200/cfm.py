@@ -154,7 +154,8 @@ class CFM(nn.Module):
             t_start = t_inter
             y0 = (1 - t_start) * y0 + t_start * test_cond
             steps = int(steps * (1 - t_start))
-        t = sway_time_grid(steps, sway_sampling_coef, device, torch.float32, use_epss, t_start)
+        # the grid is consumed as host floats by the C ABI: built on the CPU (no device launches, no D2H sync)
+        t = sway_time_grid(steps, sway_sampling_coef, "cpu", torch.float32, use_epss, t_start)
 
         return dict(cond=cond, cond_mask=cond_mask, step_cond=step_cond, text=text, duration=duration, y0=y0, t=t,
                     steps=steps, has_mask=has_mask)
@@ -167,7 +168,8 @@ class CFM(nn.Module):
         """Same arguments and results as the reference's `CFM.sample` (cfm.py:84-229).  Two keyword-only extras:
         `y0` injects the initial noise (parity tests feed the oracle's CPU noise), `return_trajectory=False` skips
         materialising the [steps+1, b, n, d] trajectory (the reference always builds it)."""
-        self.eval()
+        if self.training:  # (nn.Module.eval() walks all 421 sub-modules: ~1 ms of Python per call when done blindly)
+            self.eval()
         p = self.prepare_inputs(cond, text, duration, lens=lens, steps=steps, sway_sampling_coef=sway_sampling_coef,
                                 seed=seed, max_duration=max_duration, use_epss=use_epss, no_ref_audio=no_ref_audio,
                                 duplicate_test=duplicate_test, t_inter=t_inter, edit_mask=edit_mask, y0=y0)

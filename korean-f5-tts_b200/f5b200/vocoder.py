@@ -50,8 +50,14 @@ class Vocos(nn.Module):
         return super().load_state_dict(keep, strict=strict, **kw)
 
     def _signature(self):
-        ps = list(self.parameters())
+        ps = getattr(self, "_ps", None)  # cached Parameter list, dropped by _apply (see backbones._signature)
+        if ps is None:
+            ps = self._ps = list(self.parameters())
         return (str(ps[0].device), self.precision, tuple(p._version for p in ps), tuple(p.data_ptr() for p in ps))
+
+    def _apply(self, fn, *args, **kwargs):
+        self._ps = None
+        return super()._apply(fn, *args, **kwargs)
 
     def _drop(self):
         if getattr(self, "_handle", None):

@@ -8,6 +8,7 @@ from .modules import MelSpec  # noqa: F401
 from .utils import (get_epss_timesteps, lens_to_mask, list_str_to_idx, list_str_to_tensor,  # noqa: F401
                     seed_everything, sway_time_grid)
 from .vocoder import Vocos, load_vocoder  # noqa: F401
+from .infer import infer_batch_process  # noqa: F401
 
 __all__ = ["CFM", "DiT", "UNetT", "MelSpec", "Vocos", "load_vocoder", "lens_to_mask", "list_str_to_idx",
-           "list_str_to_tensor", "get_epss_timesteps", "sway_time_grid", "seed_everything", "F5BError"]
+           "list_str_to_tensor", "get_epss_timesteps", "sway_time_grid", "seed_everything", "F5BError", "infer_batch_process"]

@@ -1,0 +1,158 @@
+"""Request level of the path: `infer_batch_process` with the reference's signature and results
+(src/f5_tts/infer/utils_infer.py:500-770), but every text chunk of the request goes through ONE variable-length
+`CFM.sample` batch (padded masks, per-row durations) instead of a thread pool of batch-1 calls that share the
+backbone's text cache (`utils_infer.py:725-727`, `backbones/dit.py:181,259-269`).
+
+What stays host-side Python, exactly as in the reference: channel mix-down, RMS normalisation, the duration rule
+(`utils_infer.py:619-626`), tokenisation (a callable handed in by the caller: the reference's `convert_char_to_*`
+functions work unchanged), RMS rescale of the result and the linear cross-fade (`utils_infer.py:734-770`).
+The mel front end, the ODE and the Vocos decode run in libf5b200.so; nothing here computes them on the CPU."""
+from __future__ import annotations
+
+from typing import Callable, Iterable, List, Sequence
+
+import numpy as np
+import torch
+
+from .sharding import micro_batches
+from .utils import list_str_to_idx, list_str_to_tensor
+
+target_sample_rate = 24000  # utils_infer.py:62-66
+hop_length = 256
+TARGET_RMS = 0.1
+CROSS_FADE_DURATION = 0.15
+
+
+def chunk_duration(ref_audio_len: int, ref_text: str, gen_text: str, speed: float = 1.0, fix_duration=None) -> int:
+    """Frames of prompt + generated speech for one chunk (utils_infer.py:541-545, 619-626): utf-8 byte lengths,
+    texts under 10 bytes are slowed to 0.3."""
+    if fix_duration is not None:
+        return int(fix_duration * target_sample_rate / hop_length)
+    local_speed = 0.3 if len(gen_text.encode("utf-8")) < 10 else speed
+    ref_text_len = len(ref_text.encode("utf-8"))
+    gen_text_len = len(gen_text.encode("utf-8"))
+    return ref_audio_len + int(ref_audio_len / ref_text_len * gen_text_len / local_speed)
+
+
+def cross_fade(waves: Sequence[np.ndarray], cross_fade_duration: float = CROSS_FADE_DURATION,
+               sample_rate: int = target_sample_rate) -> np.ndarray:
+    """Join chunk waveforms with a linear cross-fade (utils_infer.py:734-770); plain concatenation when the duration
+    is <= 0 or a chunk is empty."""
+    if cross_fade_duration <= 0:
+        return np.concatenate(list(waves))
+    final = waves[0]
+    for nxt in waves[1:]:
+        n = min(int(cross_fade_duration * sample_rate), len(final), len(nxt))
+        if n <= 0:
+            final = np.concatenate([final, nxt])
+            continue
+        fade_out = np.linspace(1, 0, n)
+        fade_in = np.linspace(0, 1, n)
+        final = np.concatenate([final[:-n], final[-n:] * fade_out + nxt[:n] * fade_in, nxt[n:]])
+    return final
+
+
+def prepare_ref_audio(ref_audio, target_rms: float = TARGET_RMS):
+    """Mono mix, RMS lift, resample to 24 kHz (utils_infer.py:523-533).  Returns (audio [1, nw] float32, rms)."""
+    audio, sr = ref_audio
+    if audio.shape[0] > 1:
+        audio = torch.mean(audio, dim=0, keepdim=True)
+    rms = torch.sqrt(torch.mean(torch.square(audio)))
+    if rms < target_rms:
+        audio = audio * target_rms / rms
+    if sr != target_sample_rate:
+        import torchaudio
+
+        audio = torchaudio.transforms.Resample(sr, target_sample_rate)(audio)
+    return audio.to(torch.float32), float(rms)
+
+
+def _char_tokens(text_list: List[str]) -> List[List[str]]:
+    return [list(t) for t in text_list]
+
+
+def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str], model_obj, vocoder,
+                        mel_spec_type="vocos", progress=None, target_rms=TARGET_RMS,
+                        cross_fade_duration=CROSS_FADE_DURATION, nfe_step=32, cfg_strength=2.0, sway_sampling_coef=-1,
+                        speed=1, fix_duration=None, device=None, streaming=False, chunk_size=2048, *,
+                        tokenize: Callable[[List[str]], List[List[str]]] | None = None, max_rows: int = 32768,
+                        max_batch: int = 64):
+    """Generator with the reference's contract: yields `(final_wave, 24000, combined_spectrogram)` once (or
+    `(chunk, 24000)` pieces when `streaming`).  Keyword-only extras: `tokenize` (list[str] -> list[list[str]], the
+    reference's `convert_char_to_*`; characters by default), `max_rows` / `max_batch` (micro-batch limits in padded
+    frames / utterances).
+
+    Chunks are grouped into length-sorted micro-batches and each group is ONE `sample()`; rows of different length
+    need the backbone's key mask (`attn_mask_enabled=True`) to equal their batch-1 results, so a backbone built without
+    it gets one chunk per `sample()` call (same kernels, batch 1).  Noise rows are drawn chunk by chunk from the
+    global generator in request order, i.e. the stream of `torch.randn` calls is that of the reference's sequential
+    (streaming) loop."""
+    if mel_spec_type != "vocos":
+        raise ValueError("only the Vocos mel / vocoder pair is built (BigVGAN is out of scope)")
+    gen_text_batches = list(gen_text_batches)
+    device = device if device is not None else model_obj.device
+    audio, rms = prepare_ref_audio(ref_audio, target_rms)
+    audio = audio.to(device)
+    if len(ref_text[-1].encode("utf-8")) == 1:
+        ref_text = ref_text + " "
+    tokenize = tokenize or _char_tokens
+
+    if not gen_text_batches:
+        yield None, target_sample_rate, None
+        return
+
+    ref_audio_len = audio.shape[-1] // hop_length
+    durations = [chunk_duration(ref_audio_len, ref_text, g, speed, fix_duration) for g in gen_text_batches]
+    tokens = tokenize([ref_text + g for g in gen_text_batches])
+    vocab = getattr(model_obj, "vocab_char_map", None)
+    ids = [(list_str_to_idx([t], vocab) if vocab is not None else list_str_to_tensor([t]))[0] for t in tokens]
+
+    # prompt mel once per request (the reference recomputes it inside every sample() call, cfm.py:106-109)
+    ref_mel = model_obj.mel_spec(audio).permute(0, 2, 1).to(torch.float32)  # [1, T, 100]
+    n_ch = ref_mel.shape[-1]
+    # the effective length of a row after cfm.py:135-137
+    eff = [max(max(int(len(i)), ref_mel.shape[1]) + 1, d) for i, d in zip(ids, durations)]
+
+    # noise in request order (cfm.py:196-201 with seed None)
+    noise = [torch.randn(e, n_ch, device=device, dtype=torch.float32) for e in eff]
+
+    ragged_ok = bool(getattr(model_obj.transformer, "attn_mask_enabled", False))
+    order = list(range(len(eff)))
+    if ragged_ok:
+        groups = micro_batches(order, eff, max_rows=max_rows, max_batch=max_batch)
+    else:  # equal-length rows may still share a batch
+        by_len: dict = {}
+        for i in order:
+            by_len.setdefault(eff[i], []).append(i)
+        groups = [g[k:k + max_batch] for g in by_len.values() for k in range(0, len(g), max_batch)]
+
+    mels: List[torch.Tensor | None] = [None] * len(eff)
+    waves: List[np.ndarray | None] = [None] * len(eff)
+    for g in (progress.tqdm(groups) if progress is not None else groups):
+        b, n = len(g), max(eff[i] for i in g)
+        nt = max(len(ids[i]) for i in g)
+        text = torch.full((b, nt), -1, dtype=torch.long)
+        y0 = torch.zeros((b, n, n_ch), device=device, dtype=torch.float32)
+        for r, i in enumerate(g):
+            text[r, :len(ids[i])] = ids[i]
+            y0[r, :eff[i]] = noise[i]
+        dur = torch.tensor([durations[i] for i in g], device=device, dtype=torch.long)
+        with torch.inference_mode():
+            out, _ = model_obj.sample(cond=ref_mel.expand(b, -1, -1).contiguous(), text=text.to(device),
+                                      duration=dur if b > 1 else int(dur[0]), steps=nfe_step,
+                                      cfg_strength=cfg_strength, sway_sampling_coef=sway_sampling_coef, y0=y0,
+                                      return_trajectory=False)
+            for r, i in enumerate(g):
+                gen = out[r:r + 1, ref_audio_len:eff[i], :].to(torch.float32).permute(0, 2, 1).contiguous()
+                wav = vocoder.decode(gen)
+                if rms < target_rms:
+                    wav = wav * rms / target_rms
+                waves[i] = wav.squeeze().cpu().numpy()
+                mels[i] = gen[0].cpu().numpy()
+
+    if streaming:
+        for w in waves:
+            for j in range(0, len(w), chunk_size):
+                yield w[j:j + chunk_size], target_sample_rate
+        return
+    yield cross_fade(waves, cross_fade_duration), target_sample_rate, np.concatenate(mels, axis=1)

@@ -1,0 +1,79 @@
+"""the request level (`infer_batch_process`) -- all text chunks of a request as one
+variable-length batch.  CPU: host logic against the oracle's restatement of utils_infer.py.  GPU: the batched request
+against the oracle running the reference's chunk-by-chunk loop on the same audio, text and noise."""
+import numpy as np
+import pytest
+import torch
+
+from f5b200 import infer as R
+from helpers import O, build_cfm, max_abs
+
+VOCAB = {c: i for i, c in enumerate(" abcdefghijklmnopqrstuvwxyz,.?!")}
+
+
+@pytest.mark.parametrize("ref_len,ref,gen,speed,fix", [(282, "some call me nature. ", "hello there, how are you today?", 1.0, None),
+                                                       (282, "안녕하세요. ", "짧다", 1.0, None),  # < 10 bytes -> 0.3
+                                                       (100, "abc. ", "a much longer sentence than the prompt was.", 0.7, None),
+                                                       (100, "abc. ", "ignored", 1.0, 4.0)])
+def test_duration_rule(ref_len, ref, gen, speed, fix):
+    assert R.chunk_duration(ref_len, ref, gen, speed, fix) == O.request_duration(ref_len, ref, gen, speed, fix)
+
+
+@pytest.mark.parametrize("dur", [0.15, 0.0, 10.0])
+def test_cross_fade_matches_oracle(dur):
+    rng = np.random.default_rng(0)
+    waves = [rng.standard_normal(n).astype(np.float32) for n in (9000, 2000, 5000, 0 if dur == 10.0 else 3000)]
+    a, b = R.cross_fade(waves, dur), O.linear_cross_fade(waves, dur)
+    assert a.shape == b.shape and np.array_equal(a, b)
+    if dur == 0.15:
+        assert len(a) == sum(map(len, waves)) - (2000 + 3600 + 3000)  # overlap clipped to the shorter chunk
+
+
+def test_prepare_ref_audio_mix_and_rms():
+    torch.manual_seed(0)
+    stereo = torch.randn(2, 24000) * 0.01
+    audio, rms = R.prepare_ref_audio((stereo, 24000))
+    mono = stereo.mean(0, keepdim=True)
+    assert audio.shape == (1, 24000) and abs(rms - float(mono.pow(2).mean().sqrt())) < 1e-9
+    assert abs(float(audio.pow(2).mean().sqrt()) - 0.1) < 1e-6
+    loud, rms2 = R.prepare_ref_audio((torch.randn(1, 24000), 24000))
+    assert rms2 > 0.1 and abs(float(loud.pow(2).mean().sqrt()) - rms2) < 1e-6  # not attenuated
+
+
+def test_empty_request_yields_none():
+    class _M:
+        device = "cpu"
+    assert list(R.infer_batch_process((torch.randn(1, 2400) * 0.01, 24000), "a. ", [], _M(), None)) == [(None, 24000, None)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mask_enabled", [True, False])
+def test_batched_request_vs_oracle_chunk_loop(mask_enabled):
+    import f5b200
+
+    cfg = O.ArchCfg.named("F5TTS_v1_Base", depth=2, attn_mask_enabled=mask_enabled, text_num_embeds=len(VOCAB))
+    sd = O.synth_backbone_weights(cfg, seed=11)
+    vsd = O.synth_vocos_weights(3)
+    torch.manual_seed(5)
+    audio = torch.randn(1, 24000) * 0.03  # 1 s prompt, rms < 0.1 -> lifted and rescaled back
+    ref_text = "the quick brown fox."
+    gens = ["jumps over the lazy dog, twice.", "ok?", "and then it sleeps for a while, does it not?", "jumps over the lazy dog, thrice"]
+    cfm = build_cfm(cfg, sd, "fp32")
+    cfm.vocab_char_map = VOCAB
+    voc = f5b200.Vocos(precision="fp32")
+    voc.load_state_dict(vsd)
+    voc = voc.cuda()
+
+    torch.manual_seed(21)
+    (wave, sr, spec), = list(R.infer_batch_process((audio, 24000), ref_text, gens, cfm, voc, nfe_step=4, cfg_strength=2.0,
+                                                   sway_sampling_coef=-1.0))
+    # the same noise stream, chunk by chunk in request order
+    ref_len = 24000 // 256
+    torch.manual_seed(21)
+    durs = [max(O.request_duration(ref_len, ref_text + " ", g), len(ref_text + " " + g) + 1, ref_len + 2) for g in gens]
+    noises = [torch.randn(d, 100, device="cuda").cpu() for d in durs]
+    want_wave, want_spec = O.infer_request(sd, cfg, vsd, audio, ref_text, gens, VOCAB, noises, steps=4)
+    assert sr == 24000 and wave.shape == want_wave.shape and spec.shape == want_spec.shape
+    e_mel, e_wav = max_abs(spec, want_spec), max_abs(wave, want_wave)
+    print(f"request level (attn mask {mask_enabled}): mel max-abs {e_mel:.3e}, wave max-abs {e_wav:.3e}")
+    assert e_mel <= 1e-3 and e_wav <= 1e-3

@@ -100,6 +100,16 @@ int f5b_cfm_loss(f5b_plan* plan, const float* x1, const float* x0, const int64_t
 /* Replaces MelSpec.forward (model/modules.py:78-104,133-146): wav [B, nw] -> mel [B, 100, nw/256 + 1]. */
 int f5b_mel(const float* wav, int32_t B, int32_t nw, float* mel, int32_t device, int32_t mem, void* stream);
 
+/* Replaces the reference-audio preparation of infer_batch_process (infer/utils_infer.py:523-533): channel mix-down,
+ * rms = sqrt(mean(mono^2)), gain = target_rms / rms when rms < target_rms (else 1; target_rms <= 0 disables it), and
+ * torchaudio.transforms.Resample(sr, 24000) as a strided FIR: out[f * n_new + j] = gain * sum_k table[j][k] *
+ * xpad[f * n_orig + k], xpad = mono zero-padded by `width` in front.  wav [channels, nw]; table [n_new, taps] (the
+ * caller's windowed-sinc filter bank, taps = 2 * width + n_orig; {1.0} with n_new = n_orig = taps = 1, width = 0 when
+ * the rate already matches); out [out_len]; *rms_host (may be NULL) receives the measured rms. */
+int f5b_ref_audio(const float* wav, int32_t channels, int64_t nw, const float* table, int32_t n_new, int32_t taps,
+                  int32_t n_orig, int32_t width, float target_rms, float* out, int64_t out_len, float* rms_host,
+                  int32_t device, int32_t mem, void* stream);
+
 /* Replaces load_vocoder("vocos") + Vocos.decode (infer/utils_infer.py:114-137,703): mel [B,100,T] -> wav [B,(T-1)*256]. */
 int f5b_vocos_create(const f5b_tensor* weights, int32_t n_weights, int32_t mode, int32_t device, f5b_vocos** out);
 void f5b_vocos_destroy(f5b_vocos* v);

@@ -5,6 +5,7 @@
 // not depend on the ODE state is hoisted out of the NFE loop: the time embedding and all AdaLN modulation vectors
 // for every step are one skinny GEMM, the text embeddings are computed once per call, the cond/text columns of the
 // input-projection operand are written once.  The whole call is captured into one CUDA graph per shape key.
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -110,9 +111,10 @@ struct f5b_plan {
   bool cache_valid = false;
   int cache_key[6] = {0, 0, 0, 0, 0, 0};
   // graph cache
-  GraphKey gkey;
-  cudaGraphExec_t gexec = nullptr;
-  long long gnodes = 0;
+  // instantiated sampling graphs, least recently used first; all of them point into the current arena
+  struct GraphEntry { GraphKey key; cudaGraphExec_t exec; long long nodes; };
+  std::vector<GraphEntry> gcache;
+  static constexpr size_t kGraphCacheMax = 8;
   long long last_call_launches = 0;
   bool use_graph = true;
   cudaStream_t own_stream = nullptr;  // used when the caller passes the (uncapturable) legacy default stream
@@ -130,9 +132,8 @@ struct f5b_plan {
   template <typename T> void sample_body(cudaStream_t st, int B, int N, int nt, bool has_lens, const float* t_host,
                                          int steps, float cfg, bool want_traj);
   void drop_graph() {
-    if (gexec) cudaGraphExecDestroy(gexec);
-    gexec = nullptr;
-    gkey = GraphKey();
+    for (auto& e : gcache) cudaGraphExecDestroy(e.exec);
+    gcache.clear();
   }
 };
 

@@ -3,7 +3,8 @@
 `CFM.sample` batch (padded masks, per-row durations) instead of a thread pool of batch-1 calls that share the
 backbone's text cache (`utils_infer.py:725-727`, `backbones/dit.py:181,259-269`).
 
-What stays host-side Python, exactly as in the reference: channel mix-down, RMS normalisation, the duration rule
+The reference-audio preparation (row f2: channel mix-down, RMS lift, resampling to 24 kHz) is one library call,
+`f5b_ref_audio`.  What stays host-side Python, exactly as in the reference: the duration rule
 (`utils_infer.py:619-626`), tokenisation (a callable handed in by the caller: the reference's `convert_char_to_*`
 functions work unchanged), RMS rescale of the result and the linear cross-fade (`utils_infer.py:734-770`).
 The mel front end, the ODE and the Vocos decode run in libf5b200.so; nothing here computes them on the CPU."""
@@ -52,19 +53,57 @@ def cross_fade(waves: Sequence[np.ndarray], cross_fade_duration: float = CROSS_F
     return final
 
 
-def prepare_ref_audio(ref_audio, target_rms: float = TARGET_RMS):
-    """Mono mix, RMS lift, resample to 24 kHz (utils_infer.py:523-533).  Returns (audio [1, nw] float32, rms)."""
-    audio, sr = ref_audio
-    if audio.shape[0] > 1:
-        audio = torch.mean(audio, dim=0, keepdim=True)
-    rms = torch.sqrt(torch.mean(torch.square(audio)))
-    if rms < target_rms:
-        audio = audio * target_rms / rms
-    if sr != target_sample_rate:
-        import torchaudio
+def sinc_filter_bank(orig_freq: int, new_freq: int, lowpass_filter_width: int = 6, rolloff: float = 0.99):
+    """The filter bank of `torchaudio.transforms.Resample(orig, new)` with its defaults (Hann-windowed sinc, width 6,
+    roll-off 0.99; third-party torchaudio `functional._get_sinc_resample_kernel`, the reference's call is
+    utils_infer.py:530-532): float64 construction, float32 result [n_new, 2 * width + n_orig].  Host-side, cached."""
+    import math
 
-        audio = torchaudio.transforms.Resample(sr, target_sample_rate)(audio)
-    return audio.to(torch.float32), float(rms)
+    g = math.gcd(int(orig_freq), int(new_freq))
+    o, n = int(orig_freq) // g, int(new_freq) // g
+    base_freq = min(o, n) * rolloff
+    width = math.ceil(lowpass_filter_width * o / base_freq)
+    idx = torch.arange(-width, width + o, dtype=torch.float64)[None, None] / o
+    # (the phase offsets pass through float32 there: integer arange / int, then promoted by the float64 `idx`)
+    t = (torch.arange(0, -n, -1)[:, None, None] / n).to(torch.float32) + idx
+    t = (t * base_freq).clamp_(-lowpass_filter_width, lowpass_filter_width)
+    window = torch.cos(t * math.pi / lowpass_filter_width / 2) ** 2
+    t = t * math.pi
+    scale = base_freq / o
+    bank = torch.where(t == 0, torch.tensor(1.0, dtype=torch.float64), t.sin() / t) * window * scale
+    return bank.to(torch.float32).reshape(n, 2 * width + o).contiguous(), o, n, width
+
+
+_BANKS: dict = {}
+
+
+def prepare_ref_audio(ref_audio, target_rms: float = TARGET_RMS, device=None):
+    """Mono mix, RMS lift, resample to 24 kHz (utils_infer.py:523-533) in ONE library call (`f5b_ref_audio`): the
+    waveform crosses to the device once, at its original rate.  Returns (audio [1, nw24] float32 on `device`, rms)."""
+    import ctypes as C
+
+    from . import _lib
+
+    audio, sr = ref_audio
+    if audio.ndim == 1:
+        audio = audio[None]
+    dev = torch.device(device if device is not None else (audio.device if audio.is_cuda else "cuda"))
+    _lib.device_index(dev)  # no CPU fallback: a non-CUDA device is an error
+    wav = audio.to(torch.float32).to(dev, non_blocking=True).contiguous()
+    ch, nw = wav.shape
+    key = (int(sr), str(dev))
+    if key not in _BANKS:
+        bank, o, n, width = (sinc_filter_bank(sr, target_sample_rate) if sr != target_sample_rate
+                             else (torch.ones(1, 1), 1, 1, 0))
+        _BANKS[key] = (bank.to(dev), o, n, width)
+    bank, o, n, width = _BANKS[key]
+    out_len = -(-n * nw // o)  # ceil(new * length / orig), torchaudio _apply_sinc_resample_kernel
+    out = torch.empty((1, out_len), device=dev, dtype=torch.float32)
+    rms = C.c_float(0.0)
+    _lib.check(_lib.lib().f5b_ref_audio(wav.data_ptr(), ch, nw, bank.data_ptr(), n, bank.shape[1], o, width,
+                                        float(target_rms), out.data_ptr(), out_len, C.byref(rms),
+                                        _lib.device_index(dev), _lib.MEM_DEVICE, _lib.current_stream_ptr(dev)))
+    return out, float(rms.value)
 
 
 def _char_tokens(text_list: List[str]) -> List[List[str]]:
@@ -75,7 +114,7 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
                         mel_spec_type="vocos", progress=None, target_rms=TARGET_RMS,
                         cross_fade_duration=CROSS_FADE_DURATION, nfe_step=32, cfg_strength=2.0, sway_sampling_coef=-1,
                         speed=1, fix_duration=None, device=None, streaming=False, chunk_size=2048, *,
-                        tokenize: Callable[[List[str]], List[List[str]]] | None = None, max_rows: int = 32768,
+                        tokenize: Callable[[List[str]], List[List[str]]] | None = None, max_rows: int = 16384,
                         max_batch: int = 64):
     """Generator with the reference's contract: yields `(final_wave, 24000, combined_spectrogram)` once (or
     `(chunk, 24000)` pieces when `streaming`).  Keyword-only extras: `tokenize` (list[str] -> list[list[str]], the
@@ -91,15 +130,13 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
         raise ValueError("only the Vocos mel / vocoder pair is built (BigVGAN is out of scope)")
     gen_text_batches = list(gen_text_batches)
     device = device if device is not None else model_obj.device
-    audio, rms = prepare_ref_audio(ref_audio, target_rms)
-    audio = audio.to(device)
-    if len(ref_text[-1].encode("utf-8")) == 1:
-        ref_text = ref_text + " "
-    tokenize = tokenize or _char_tokens
-
     if not gen_text_batches:
         yield None, target_sample_rate, None
         return
+    audio, rms = prepare_ref_audio(ref_audio, target_rms, device)
+    if len(ref_text[-1].encode("utf-8")) == 1:
+        ref_text = ref_text + " "
+    tokenize = tokenize or _char_tokens
 
     ref_audio_len = audio.shape[-1] // hop_length
     durations = [chunk_duration(ref_audio_len, ref_text, g, speed, fix_duration) for g in gen_text_batches]

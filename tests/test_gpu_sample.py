@@ -99,6 +99,36 @@ def test_host_buffers_and_graph_replay():
     assert max_abs(a, c) <= 1e-4
 
 
+def test_graph_cache_many_shapes():
+    """The plan keeps a small LRU of instantiated sampling graphs (one per shape / grid): revisiting a shape replays
+    its graph with the same bits, also after the cache has cycled through more shapes than it holds and after the
+    workspace grew (which drops every graph)."""
+    cfg = O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2)
+    sd = O.synth_backbone_weights(cfg, seed=2)
+    cfm = build_cfm(cfg, sd, "fp32")
+    g = torch.Generator().manual_seed(8)
+    shapes = [96 - 4 * k for k in range(11)]  # largest first: no workspace growth until the last case
+    data = {n: (O.synth_inputs(n, 20, 7, seed=n), torch.randn(1, n, 100, generator=g)) for n in shapes + [120]}
+
+    def run(n, steps=4):
+        (cond, text), y0 = data[n]
+        return cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, duration=n, steps=steps, cfg_strength=2.0,
+                          sway_sampling_coef=-1.0, return_trajectory=False)[0]
+
+    first = {n: run(n) for n in shapes}
+    for n in (shapes[0], shapes[-1], shapes[3], shapes[0]):  # evicted, cached, evicted, cached
+        assert torch.equal(run(n), first[n])
+    ref = O.cfm_sample(sd, cfg, *data[shapes[3]][0], shapes[3], steps=4, cfg_strength=2.0, sway_sampling_coef=-1.0,
+                       y0=data[shapes[3]][1])
+    assert max_abs(first[shapes[3]].cpu(), ref.out) <= 1e-3
+    other = run(shapes[3], steps=6)  # same shape, other grid: its own graph
+    assert not torch.equal(other, first[shapes[3]])
+    run(120)  # grows the workspace
+    for n in (shapes[3], shapes[0]):
+        assert torch.equal(run(n), first[n])
+
+
+
 def test_mel_frontend_golden(golden_dir):
     import f5b200
 

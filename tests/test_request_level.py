@@ -29,15 +29,40 @@ def test_cross_fade_matches_oracle(dur):
         assert len(a) == sum(map(len, waves)) - (2000 + 3600 + 3000)  # overlap clipped to the shorter chunk
 
 
-def test_prepare_ref_audio_mix_and_rms():
-    torch.manual_seed(0)
-    stereo = torch.randn(2, 24000) * 0.01
-    audio, rms = R.prepare_ref_audio((stereo, 24000))
-    mono = stereo.mean(0, keepdim=True)
-    assert audio.shape == (1, 24000) and abs(rms - float(mono.pow(2).mean().sqrt())) < 1e-9
-    assert abs(float(audio.pow(2).mean().sqrt()) - 0.1) < 1e-6
-    loud, rms2 = R.prepare_ref_audio((torch.randn(1, 24000), 24000))
-    assert rms2 > 0.1 and abs(float(loud.pow(2).mean().sqrt()) - rms2) < 1e-6  # not attenuated
+@pytest.mark.parametrize("sr", [44100, 22050, 16000, 48000, 8000])
+def test_sinc_filter_bank_is_torchaudio_s(sr):
+    """The host-built filter bank equals the one torchaudio.transforms.Resample holds (the reference's call)."""
+    import torchaudio
+
+    ref = torchaudio.transforms.Resample(sr, 24000)
+    bank, o, n, width = R.sinc_filter_bank(sr, 24000)
+    assert (o, n, width) == (ref.orig_freq // ref.gcd, ref.new_freq // ref.gcd, ref.width)
+    assert torch.equal(bank, ref.kernel.reshape(n, -1))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sr,ch,nw,scale", [(44100, 2, 132300, 0.02), (24000, 1, 72000, 0.02), (16000, 1, 50001, 0.5),
+                                            (48000, 2, 96000, 0.01), (22050, 1, 4097, 0.03), (8000, 3, 777, 0.05)])
+def test_ref_audio_front_half_vs_torchaudio(sr, ch, nw, scale):
+    """f5b_ref_audio (mix-down + rms lift + polyphase resampler) against the reference's torch / torchaudio calls."""
+    g = torch.Generator().manual_seed(nw)
+    wav = torch.randn(ch, nw, generator=g) * scale
+    want, want_rms = O.prepare_ref_audio(wav, sr)
+    got, rms = R.prepare_ref_audio((wav, sr), device="cuda")
+    assert got.shape == want.shape
+    err = max_abs(got, want)
+    print(f"ref audio {sr} Hz x{ch}: rms {rms:.6f} vs {want_rms:.6f}, max-abs {err:.2e} (peak {float(want.abs().max()):.2f})")
+    assert abs(rms - want_rms) <= 1e-6 * max(1.0, want_rms) and err <= 2e-6 * max(1.0, float(want.abs().max()))
+    again, _ = R.prepare_ref_audio((wav.cuda(), sr))  # device input, cached filter bank: same bits
+    assert torch.equal(again, got)
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="CPU-only behaviour")
+def test_ref_audio_has_no_cpu_path():
+    from f5b200 import F5BError
+
+    with pytest.raises(F5BError):
+        R.prepare_ref_audio((torch.randn(1, 2400), 24000), device="cpu")
 
 
 def test_empty_request_yields_none():

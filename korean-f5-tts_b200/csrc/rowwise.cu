@@ -1,6 +1,5 @@
 // Memory-bound kernels of the CFM.sample path: fused, coalesced, 128-bit vectorised, warp-shuffle reductions.
 // One warp owns one row wherever a row statistic is needed (rows are 2-4 KB: the re-reads hit L1).
-#include <cstdlib>
 #include "rowwise.h"
 
 namespace f5b {
@@ -115,13 +114,9 @@ ln_mod_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int
 // Register-resident variant for d <= 1024: the row is read from memory once (8 float4 per lane).
 // LN_REG_ROWS rows (one per warp) per CTA (2-row CTAs, 940 of them at C2, measured the same step time as 8-row ones).
 static constexpr int LN_REG_ROWS = 8;
-static constexpr long long LN_STREAM_ROWS = 4096;  // from here on the streaming (high-occupancy) form is used
 
-// kPrefetchMod: hold the modulation vectors in registers across the dependency wait (batch-1 latency path, 113
-// registers, 2 CTAs / SM); otherwise they are read in the store loop (L1 / L2 hits) so that 4 CTAs / SM keep twice the
-// row loads in flight -- the streaming form for large M.  Same arithmetic, same bits.
-template <typename T, bool kPrefetchMod>
-__global__ void __launch_bounds__(32 * LN_REG_ROWS, kPrefetchMod ? 2 : 4)
+template <typename T>
+__global__ void __launch_bounds__(32 * LN_REG_ROWS)
 ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d, const float* __restrict__ mul,
                   const float* __restrict__ add, float mul_off, long long vec_bstride, int rows_per_batch, int bmod,
                   float eps) {
@@ -137,15 +132,13 @@ ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M,
   const float* ad = add ? add + b * vec_bstride : nullptr;
   float4 buf[8], g[8], h[8];
   // the modulation vectors are per-call tables (not written inside the step chain): fetched before the dependency wait
-  if (kPrefetchMod) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int c = i * 128 + lane * 4;
-      if (c < d) {
-        g[i] = mu ? __ldg(reinterpret_cast<const float4*>(mu + c))
-                  : make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
-        h[i] = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
-      }
+  for (int i = 0; i < 8; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < d) {
+      g[i] = mu ? __ldg(reinterpret_cast<const float4*>(mu + c))
+                : make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
+      h[i] = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
     }
   }
   pdl_wait();
@@ -176,11 +169,6 @@ ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M,
     const int c = i * 128 + lane * 4;
     if (c < d) {
       const float4 v = buf[i];
-      if (!kPrefetchMod) {
-        g[i] = mu ? __ldg(reinterpret_cast<const float4*>(mu + c))
-                  : make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
-        h[i] = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
-      }
       RowOut<T>::st(orow, c, d, (v.x - mean) * rstd * (mul_off + g[i].x) + h[i].x,
                     (v.y - mean) * rstd * (mul_off + g[i].y) + h[i].y,
                     (v.z - mean) * rstd * (mul_off + g[i].z) + h[i].z,
@@ -194,12 +182,8 @@ template <typename T>
 void ln_mod(cudaStream_t st, const float* x, T* out, long long M, int d, const float* mul, const float* add,
             float mul_off, long long vec_bstride, int rows_per_batch, int bmod, float eps) {
   F5B_REQUIRE(d % 4 == 0, "LayerNorm width must be a multiple of 4");
-  static const bool ln_stream = std::getenv("F5B_LN_STREAM") != nullptr;  // opt-in until measured on the GPU
-  if (d <= 1024 && ln_stream && M >= LN_STREAM_ROWS)
-    launch_pdl_id(4, ln_mod_reg_kernel<T, false>, dim3(ceil_div_ll(M, LN_REG_ROWS)), dim3(32 * LN_REG_ROWS), 0, st, x, out, M, d, mul, add, mul_off,
-               vec_bstride, rows_per_batch, bmod < 1 ? 1 : bmod, eps);
-  else if (d <= 1024)
-    launch_pdl_id(4, ln_mod_reg_kernel<T, true>, dim3(ceil_div_ll(M, LN_REG_ROWS)), dim3(32 * LN_REG_ROWS), 0, st, x, out, M, d, mul, add, mul_off,
+  if (d <= 1024)
+    launch_pdl_id(4, ln_mod_reg_kernel<T>, dim3(ceil_div_ll(M, LN_REG_ROWS)), dim3(32 * LN_REG_ROWS), 0, st, x, out, M, d, mul, add, mul_off,
                vec_bstride, rows_per_batch, bmod < 1 ? 1 : bmod, eps);
   else
     ln_mod_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride, rows_per_batch,

@@ -8,6 +8,7 @@ from .modules import MelSpec  # noqa: F401
 from .utils import (get_epss_timesteps, lens_to_mask, list_str_to_idx, list_str_to_tensor,  # noqa: F401
                     seed_everything, sway_time_grid)
 from .vocoder import Vocos, load_vocoder  # noqa: F401
+from . import tokenizers  # noqa: F401
 from .infer import infer_batch_process  # noqa: F401
 from .checkpoint import get_tokenizer, load_checkpoint, load_model  # noqa: F401
 from .api import F5TTS, chunk_text, infer_process  # noqa: F401

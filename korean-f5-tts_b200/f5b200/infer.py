@@ -15,6 +15,7 @@ from typing import Callable, Iterable, List, Sequence
 import numpy as np
 import torch
 
+from . import tokenizers
 from .sharding import micro_batches
 from .utils import list_str_to_idx, list_str_to_tensor
 
@@ -106,10 +107,6 @@ def prepare_ref_audio(ref_audio, target_rms: float = TARGET_RMS, device=None):
     return out, float(rms.value)
 
 
-def _char_tokens(text_list: List[str]) -> List[List[str]]:
-    return [list(t) for t in text_list]
-
-
 def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str], model_obj, vocoder,
                         mel_spec_type="vocos", progress=None, target_rms=TARGET_RMS,
                         cross_fade_duration=CROSS_FADE_DURATION, nfe_step=32, cfg_strength=2.0, sway_sampling_coef=-1,
@@ -117,8 +114,9 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
                         tokenize: Callable[[List[str]], List[List[str]]] | None = None, max_rows: int = 16384,
                         max_batch: int = 64):
     """Generator with the reference's contract: yields `(final_wave, 24000, combined_spectrogram)` once (or
-    `(chunk, 24000)` pieces when `streaming`).  Keyword-only extras: `tokenize` (list[str] -> list[list[str]], the
-    reference's `convert_char_to_*`; characters by default), `max_rows` / `max_batch` (micro-batch limits in padded
+    `(chunk, 24000)` pieces when `streaming`).  Keyword-only extras: `tokenize` (list[str] -> list[list[str]]; by default the
+    reference's `convert_char_to_*` picked by the reference's rule from `model_obj._tokenizer_type / _use_skip_tc /
+    _use_n2gk_plus` and the vocabulary, `f5b200.tokenizers`), `max_rows` / `max_batch` (micro-batch limits in padded
     frames / utterances).
 
     Chunks are grouped into length-sorted micro-batches and each group is ONE `sample()`; rows of different length
@@ -136,7 +134,8 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
     audio, rms = prepare_ref_audio(ref_audio, target_rms, device)
     if len(ref_text[-1].encode("utf-8")) == 1:
         ref_text = ref_text + " "
-    tokenize = tokenize or _char_tokens
+    if tokenize is None:  # the reference's rule (utils_infer.py:549-676); raises when its converters are not importable
+        tokenize = tokenizers.resolve(tokenizers.choose_for_model(model_obj))
 
     ref_audio_len = audio.shape[-1] // hop_length
     durations = [chunk_duration(ref_audio_len, ref_text, g, speed, fix_duration) for g in gen_text_batches]

@@ -61,7 +61,8 @@ def test_f5tts_infer_from_files_vs_oracle(tmp_path):
         w.setnchannels(2); w.setsampwidth(2); w.setframerate(16000); w.writeframes(pcm.tobytes())
 
     tts = A.F5TTS(model=str(tmp_path / "tiny.yaml"), ckpt_file=str(tmp_path / "model.safetensors"),
-                  vocab_file=str(tmp_path / "vocab.txt"), device="cuda")
+                  vocab_file=str(tmp_path / "vocab.txt"), device="cuda",
+                  tokenize=f5b200.tokenizers.char_tokens)  # plain character vocabulary: explicit opt-in
     tts.vocoder.load_state_dict(vsd)
     tts.ema_model.transformer.float()
     tts.vocoder.precision = "fp32"

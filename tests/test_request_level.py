@@ -5,7 +5,9 @@ import numpy as np
 import pytest
 import torch
 
+import f5b200
 from f5b200 import infer as R
+from f5b200 import tokenizers as TK
 from helpers import O, build_cfm, max_abs
 
 VOCAB = {c: i for i, c in enumerate(" abcdefghijklmnopqrstuvwxyz,.?!")}
@@ -27,6 +29,69 @@ def test_cross_fade_matches_oracle(dur):
     assert a.shape == b.shape and np.array_equal(a, b)
     if dur == 0.15:
         assert len(a) == sum(map(len, waves)) - (2000 + 3600 + 3000)  # overlap clipped to the shorter chunk
+
+
+def _request_golden(golden_dir):
+    import json
+    import os
+    with open(os.path.join(golden_dir, "request_level.json"), encoding="utf-8") as f:
+        return json.load(f)
+
+
+def test_duration_rule_matches_reference_golden(golden_dir):
+    """Pinned to the reference's own statements (utils_infer.py:541-545,678-685 lifted by oracle/make_golden_request.py)."""
+    for c in _request_golden(golden_dir)["duration"]:
+        ref_len = c["n_audio"] // 256
+        assert ref_len == c["ref_audio_len"]
+        for fn in (R.chunk_duration, O.request_duration):
+            assert fn(ref_len, c["ref_text"], c["gen_text"], c["speed"], c["fix_duration"]) == c["duration"], c
+
+
+def test_cross_fade_matches_reference_golden(golden_dir):
+    """The reference's cross-fade block (utils_infer.py:734-770, lifted) on the same seeded waves, bit for bit."""
+    rng = np.random.default_rng(0)
+    for c in _request_golden(golden_dir)["cross_fade"]:
+        waves = [rng.standard_normal(n).astype(np.float32) for n in c["lens"]]
+        want = np.asarray(c["final"], dtype=np.float64)
+        for fn in (R.cross_fade, O.linear_cross_fade):
+            got = fn(waves, c["cross_fade_duration"], c["sample_rate"])
+            assert got.shape == want.shape and np.array_equal(np.asarray(got, dtype=np.float64), want), c["lens"]
+
+
+def test_tokenizer_dispatch_matches_reference_golden(golden_dir):
+    """Every (tokenizer type, vocabulary flavour, skipTC, N2gk+) combination picks the converter, the keyword arguments
+    and the normalisation the reference's dispatch (utils_infer.py:549-676, lifted) picks."""
+    from oracle.make_golden_request import VOCABS
+
+    rows = _request_golden(golden_dir)["dispatch"]
+    assert len(rows) > 300
+    for r in rows:
+        vocab = None if r["vocab"] == "none" else VOCABS[r["vocab"]]
+        ch = TK.choose(r["tokenizer_type"], vocab, r["skip_tc"], r["n2gk"], r.get("legacy", False))
+        want_norm = any(c["fn"] == "normalize_n2gk_plus" for c in r["calls"])
+        conv = [c for c in r["calls"] if c["fn"] != "normalize_n2gk_plus"]
+        assert len(conv) == 1
+        assert (ch.normalize, ch.fn, ch.kwargs) == (want_norm, conv[0]["fn"], conv[0]["kwargs"]), r
+
+
+def test_tokenizer_is_never_silently_characters():
+    """with a Korean vocabulary and no converter importable the request must fail, not emit characters."""
+    class _M:
+        device = "cpu"
+        vocab_char_map = {"k": 0, "kⁱ": 1}
+        _tokenizer_type = "custom"
+    assert TK.choose_for_model(_M()).fn == "convert_char_to_allophone"
+    if TK._reference_utils() is None:
+        with pytest.raises(RuntimeError, match="convert_char_to_allophone"):
+            TK.resolve(TK.choose_for_model(_M()))
+    # a stand-in module shows the binding: normalisation first, then the converter with the named filter constants
+    import types
+    calls = []
+    mod = types.SimpleNamespace(PHONEMES_N=["n"], normalize_n2gk_plus=lambda t: t.upper(),
+                                convert_char_to_allophone=lambda tl, **kw: calls.append((tl, kw)) or [list(t) for t in tl])
+    fn = TK.resolve(TK.choose("kor_n_only", {"a": 0}, False, True), module=mod)
+    assert fn(["ab"]) == [["A", "B"]]
+    assert calls == [(["AB"], dict(apply_init=False, apply_pal=False, apply_coda=True, coda_filter=["n"], initial_filter=None))]
 
 
 @pytest.mark.parametrize("sr", [44100, 22050, 16000, 48000, 8000])
@@ -91,7 +156,7 @@ def test_batched_request_vs_oracle_chunk_loop(mask_enabled):
 
     torch.manual_seed(21)
     (wave, sr, spec), = list(R.infer_batch_process((audio, 24000), ref_text, gens, cfm, voc, nfe_step=4, cfg_strength=2.0,
-                                                   sway_sampling_coef=-1.0))
+                                                   sway_sampling_coef=-1.0, tokenize=f5b200.tokenizers.char_tokens))
     # the same noise stream, chunk by chunk in request order
     ref_len = 24000 // 256
     torch.manual_seed(21)

@@ -26,6 +26,7 @@ extern "C" {
 #define F5B_ERR_CUDA (-2)
 #define F5B_ERR_NO_DEVICE (-3)
 #define F5B_ERR_MISSING (-4)
+#define F5B_ERR_INDEX (-5) /* a text id outside [-1, text_num_embeds): nn.Embedding raises IndexError (dit.py:42,94) */
 
 #define F5B_MEM_HOST 0
 #define F5B_MEM_DEVICE 1

@@ -107,6 +107,8 @@ struct f5b_plan {
   float *ada_w = nullptr, *ada_b = nullptr;
   int ada_W = 0;
   float *inv_freq_text, *inv_freq_rope, *time_freq;
+  int* bad_id_dev = nullptr;   // set by text_lookup on a token id outside the embedding table
+  int* bad_id_host = nullptr;  // pinned mirror, read after the call's synchronisation
   // forward-API text cache
   bool cache_valid = false;
   int cache_key[6] = {0, 0, 0, 0, 0, 0};
@@ -139,6 +141,7 @@ struct f5b_plan {
 
 f5b_plan::~f5b_plan() {
   drop_graph();
+  if (bad_id_host) cudaFreeHost(bad_id_host);
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 
@@ -266,6 +269,10 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
   inv_freq_text = warena.alloc_n<float>(ft.size() ? ft.size() : 1);
   inv_freq_rope = warena.alloc_n<float>(32);
   time_freq = warena.alloc_n<float>(128);
+  bad_id_dev = warena.alloc_n<int>(1);
+  F5B_CHECK_CUDA(cudaMemset(bad_id_dev, 0, sizeof(int)));
+  F5B_CHECK_CUDA(cudaHostAlloc(&bad_id_host, sizeof(int), cudaHostAllocDefault));
+  *bad_id_host = 0;
   if (!ft.empty()) F5B_CHECK_CUDA(cudaMemcpy(inv_freq_text, ft.data(), ft.size() * 4, cudaMemcpyHostToDevice));
   F5B_CHECK_CUDA(cudaMemcpy(inv_freq_rope, fr.data(), 32 * 4, cudaMemcpyHostToDevice));
   F5B_CHECK_CUDA(cudaMemcpy(time_freq, tf.data(), 128 * 4, cudaMemcpyHostToDevice));
@@ -285,8 +292,15 @@ void f5b_plan::ensure_ws(int B, int N, int nt, int steps, bool want_traj) {
   drop_graph();
   cache_valid = false;
   F5B_CHECK_CUDA(cudaDeviceSynchronize());
-  wk.reset(new Arena());
-  Arena& A = *wk;
+  // The old arena goes first (peak memory stays at one workspace); until every allocation below has succeeded the
+  // plan holds NO workspace and zero capacities, so a failed growth (OOM on a large request) cannot leave stale
+  // pointers behind a passing capacity check: the next call simply allocates again.
+  wk.reset();
+  bf = Bufs();
+  std::unique_ptr<Arena> fresh(new Arena());
+  Arena& A = *fresh;
+  Bufs nb;
+  Bufs& bf = nb;  // (shadows the member on purpose: everything below fills the local copy)
   const int d = a.dim, mel = a.mel_dim, ffd = a.dim * a.ff_mult;
   const size_t es = ctx.mode == F5B_MODE_BF16 ? 2 : 4;
   const int nT = steps > 2 * B ? steps : 2 * B;  // table rows: steps (sample) or B (forward)
@@ -339,7 +353,7 @@ void f5b_plan::text_embed(cudaStream_t st, int B, int N, int nt, int batches, in
                           int cond_uncond_from, const int* lens_text) {
   const bool extra = a.conv_layers > 0;
   text_lookup(st, bf.text, B, nt, text_uncond_from, batches, N, td, lens_text, emb_table,
-              extra ? inv_freq_text : nullptr, a.text_mask_padding, bf.te, bf.keep);
+              extra ? inv_freq_text : nullptr, a.text_mask_padding, bf.te, bf.keep, a.text_num_embeds + 1, bad_id_dev);
   const long long M = (long long)batches * N;
   const bool need_mask = extra && (a.text_mask_padding || lens_text != nullptr);
   for (size_t i = 0; i < tblocks.size(); ++i) {

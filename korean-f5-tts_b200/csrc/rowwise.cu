@@ -390,7 +390,7 @@ __global__ void __launch_bounds__(256)
 text_lookup_kernel(const long long* __restrict__ text, int B, int nt, int uncond_from, int batches, int rows, int td,
                    const int* __restrict__ row_len, const float* __restrict__ table,
                    const float* __restrict__ inv_freq, int mask_padding, float* __restrict__ out,
-                   unsigned char* __restrict__ keep) {
+                   unsigned char* __restrict__ keep, int table_rows, int* __restrict__ bad_id) {
   const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (m >= (long long)batches * rows) return;
@@ -399,6 +399,10 @@ text_lookup_kernel(const long long* __restrict__ text, int B, int nt, int uncond
   const int len = row_len ? row_len[b2] : rows;
   long long tok = 0;
   if (pos < nt && pos < len) tok = text[(long long)b * nt + pos] + 1;
+  if (tok < 0 || tok >= table_rows) {  // nn.Embedding raises IndexError there; here: flag it, read the filler row
+    if (lane == 0 && bad_id) *bad_id = 1;
+    tok = 0;
+  }
   const bool is_pad = tok == 0;
   if (b2 >= uncond_from) tok = 0;
   const bool exists = pos < len;
@@ -422,9 +426,10 @@ text_lookup_kernel(const long long* __restrict__ text, int B, int nt, int uncond
 }
 void text_lookup(cudaStream_t st, const long long* text, int B, int nt, int branches_uncond_from, int batches,
                  int rows, int td, const int* row_len, const float* table, const float* inv_freq, int mask_padding,
-                 float* out, unsigned char* keep) {
+                 float* out, unsigned char* keep, int table_rows, int* bad_id) {
   text_lookup_kernel<<<ceil_div_ll((long long)batches * rows, 8), 256, 0, st>>>(
-      text, B, nt, branches_uncond_from, batches, rows, td, row_len, table, inv_freq, mask_padding, out, keep);
+      text, B, nt, branches_uncond_from, batches, rows, td, row_len, table, inv_freq, mask_padding, out, keep,
+      table_rows, bad_id);
   F5B_POST_LAUNCH();
 }
 

@@ -35,7 +35,8 @@ void grn_inplace(cudaStream_t st, T* h, int batches, int rows, int C, const int*
 // table, optional padding mask.  text int64 [B, nt]; branches: b2 < B cond, b2 >= B uncond (all-zero ids) when two.
 void text_lookup(cudaStream_t st, const long long* text, int B, int nt, int branches_uncond_from, int batches,
                  int rows, int td, const int* row_len, const float* table, const float* inv_freq /* null: no pos */,
-                 int mask_padding, float* out, unsigned char* keep);
+                 int mask_padding, float* out, unsigned char* keep, int table_rows, int* bad_id /* set to 1 on an id
+                 outside the table (the reference's nn.Embedding raises IndexError); may be null */);
 void mask_rows(cudaStream_t st, float* x, long long M, int d, const unsigned char* keep);
 
 // A_in[m, 100:200) = cond (zero for the uncond branch), A_in[m, 200:200+td) = text embedding.

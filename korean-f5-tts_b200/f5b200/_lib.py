@@ -16,7 +16,7 @@ MODE_FP32, MODE_BF16 = 0, 1
 BACKBONE_DIT, BACKBONE_UNETT = 0, 1
 ACT = {"none": 0, "gelu_tanh": 1, "gelu": 2, "mish": 3, "silu": 4}
 
-ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_MISSING = -1, -2, -3, -4
+ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_MISSING, ERR_INDEX = -1, -2, -3, -4, -5
 
 
 class F5BError(RuntimeError):
@@ -94,6 +94,8 @@ def check(code: int) -> None:
         raise ValueError(msg)
     if code == ERR_MISSING:
         raise KeyError(msg)
+    if code == ERR_INDEX:
+        raise IndexError(msg)
     raise F5BError(f"libf5b200 error {code}: {msg}")
 
 

@@ -110,7 +110,7 @@ def infer_process(ref_audio, ref_text, gen_text, model_obj, vocoder, mel_spec_ty
 class F5TTS:
     def __init__(self, model="F5TTS_v1_Base", ckpt_file="", vocab_file="", ode_method="euler", use_ema=True,
                  vocoder_local_path=None, device=None, hf_cache_dir=None, *, tokenize=None, tokenizer="custom",
-                 use_skip_tc=False, use_n2gk_plus=True):
+                 use_skip_tc=False, use_n2gk_plus=True, allow_uninitialized_vocoder=False):
         backbone, arch, self.mel_spec_type, self.target_sample_rate = model_config(model)
         for k in ("checkpoint_activations",):
             arch.pop(k, None)
@@ -120,7 +120,7 @@ class F5TTS:
         if not ckpt_file:
             raise ValueError("ckpt_file is required: the reference's hub download (api.py:76-79) needs a network")
         self.vocoder = load_vocoder(self.mel_spec_type, vocoder_local_path is not None, vocoder_local_path or "",
-                                    self.device, hf_cache_dir)
+                                    self.device, hf_cache_dir, allow_uninitialized=allow_uninitialized_vocoder)
         self.ema_model = load_model(getattr(backbones, backbone), arch, ckpt_file, self.mel_spec_type, vocab_file,
                                     self.ode_method, self.use_ema, self.device, use_skip_tc=use_skip_tc,
                                     use_n2gk_plus=use_n2gk_plus, tokenizer=tokenizer)

@@ -76,6 +76,23 @@ def _x_rmsnorm(dim: int) -> nn.Module:
     return m
 
 
+class _RotaryEmbedding(nn.Module):
+    """Holds `inv_freq` under the name the reference's state dicts carry it: x_transformers' RotaryEmbedding registers
+    it as a PERSISTENT buffer (dit.py:184, unett.py:140), so trainer-written checkpoints contain
+    `transformer.rotary_embed.inv_freq` and a strict load needs a home for it.  The library computes its own RoPE table
+    (the same fp32 expression); a checkpoint without the key (written by code that keeps the buffer non-persistent) loads
+    as well."""
+
+    def __init__(self, dim_head: int, base: float = 10000.0):
+        super().__init__()
+        self.register_buffer("inv_freq", 1.0 / (base ** (torch.arange(0, dim_head, 2).float() / dim_head)))
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        if prefix + "inv_freq" not in state_dict:
+            return
+        super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+
+
 class _PlanBackbone(nn.Module):
     """Shared plan lifecycle: parameters are fp32 masters; `precision` selects the kernel set."""
 
@@ -223,6 +240,7 @@ class DiT(_PlanBackbone):
             nn.init.constant_(blk.attn_norm.linear.weight, 0)  # dit.py:216-218
             nn.init.constant_(blk.attn_norm.linear.bias, 0)
             blocks.append(blk)
+        self.rotary_embed = _RotaryEmbedding(dim_head)
         self.transformer_blocks = nn.ModuleList(blocks)
         self.norm_out = nn.Module()
         self.norm_out.linear = nn.Linear(dim, dim * 2)
@@ -265,6 +283,7 @@ class UNetT(_PlanBackbone):
             skip = nn.Linear(dim * 2, dim, bias=False) if later else None
             layers.append(nn.ModuleList([skip, _x_rmsnorm(dim), _attention(dim, heads, dim_head, dropout),
                                          _x_rmsnorm(dim), _feed_forward(dim, ff_mult, dropout)]))
+        self.rotary_embed = _RotaryEmbedding(dim_head)
         self.layers = nn.ModuleList(layers)
         self.norm_out = _x_rmsnorm(dim)
         self.proj_out = nn.Linear(dim, mel_dim)

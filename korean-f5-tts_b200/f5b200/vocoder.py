@@ -99,17 +99,34 @@ class Vocos(nn.Module):
     forward = decode
 
 
-def load_vocoder(vocoder_name="vocos", is_local=False, local_path="", device="cuda", hf_cache_dir=None):
-    """Same signature as the reference (infer/utils_infer.py:113).  Only local Vocos checkpoints can be loaded here
-    (no network); `local_path` may also be empty, which gives the default-initialised module (benchmarks load
-    synthetic weights with `load_state_dict`)."""
+def load_vocoder(vocoder_name="vocos", is_local=False, local_path="", device="cuda", hf_cache_dir=None, *,
+                 precision: str | None = None, allow_uninitialized: bool = False):
+    """Same signature as the reference (infer/utils_infer.py:113).  The reference downloads `charactr/vocos-mel-24khz`
+    from the hub when `is_local` is False; there is no network here, so weights must come from `local_path`
+    (`pytorch_model.bin`, or a hub cache laid out under `hf_cache_dir`).  Returning a randomly initialised vocoder would
+    make `F5TTS.infer` emit noise without any error: that needs the explicit `allow_uninitialized=True`
+    (benchmarks and tests that `load_state_dict` synthetic weights afterwards).
+    `precision` None follows the backbone's rule: 16-bit tensor-core kernels on CUDA (the reference runs fp16 there,
+    utils_infer.py:243-251), fp32 kernels when asked for."""
     if vocoder_name != "vocos":
         raise ValueError("only the Vocos vocoder is built (north star); BigVGAN is out of scope")
-    voc = Vocos()
+    if precision is None:
+        precision = "bf16" if "cuda" in str(device) else "fp32"
+    voc = Vocos(precision=precision)
+    model_path = None
     if is_local and local_path:
         model_path = os.path.join(local_path, "pytorch_model.bin")
+    elif hf_cache_dir:  # a pre-populated hub cache: <cache>/models--charactr--vocos-mel-24khz/snapshots/*/pytorch_model.bin
+        import glob
+
+        hits = sorted(glob.glob(os.path.join(hf_cache_dir, "models--charactr--vocos-mel-24khz", "snapshots", "*",
+                                             "pytorch_model.bin")))
+        model_path = hits[-1] if hits else None
+    if model_path is not None:
         state = torch.load(model_path, map_location="cpu", weights_only=True)
         voc.load_state_dict(state)
-    elif not is_local and local_path == "":
-        pass  # hub download is unavailable offline; caller supplies weights
+    elif not allow_uninitialized:
+        raise FileNotFoundError("load_vocoder: no Vocos weights (the reference's hub download needs a network): pass "
+                                "is_local=True with local_path=<dir holding pytorch_model.bin>, or "
+                                "allow_uninitialized=True and load a state dict yourself")
     return voc.eval().to(device)

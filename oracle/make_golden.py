@@ -38,7 +38,9 @@ def build_reference(R, cfg: O.ArchCfg, sd):
               conv_layers=cfg.conv_layers, text_num_embeds=cfg.text_num_embeds, pe_attn_head=cfg.pe_attn_head,
               text_mask_padding=cfg.text_mask_padding, attn_mask_enabled=cfg.attn_mask_enabled, qk_norm=cfg.qk_norm)
     m = (R.DiT if cfg.backbone == "DiT" else R.UNetT)(**kw)
-    m.load_state_dict(sd, strict=True)
+    # x_transformers registers RotaryEmbedding.inv_freq as a persistent buffer (so does the shim): synthetic state dicts
+    # do not carry it, real checkpoints do
+    m.load_state_dict({**sd, "rotary_embed.inv_freq": m.rotary_embed.inv_freq}, strict=True)
     return R.CFM(transformer=m, mel_spec_kwargs=dict(mel_spec_type="vocos")).eval()
 
 

@@ -41,7 +41,7 @@ class RotaryEmbedding(nn.Module):
     def __init__(self, dim, base=10000.0):
         super().__init__()
         inv_freq = 1.0 / (base ** (torch.arange(0, dim, 2).float() / dim))
-        self.register_buffer("inv_freq", inv_freq, persistent=False)
+        self.register_buffer("inv_freq", inv_freq)  # persistent, like x_transformers': checkpoints carry the key
 
     def forward_from_seq_len(self, seq_len):
         pos = torch.arange(seq_len, device=self.inv_freq.device).type_as(self.inv_freq)

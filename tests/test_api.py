@@ -60,10 +60,13 @@ def test_f5tts_infer_from_files_vs_oracle(tmp_path):
     with wave.open(str(tmp_path / "ref.wav"), "wb") as w:
         w.setnchannels(2); w.setsampwidth(2); w.setframerate(16000); w.writeframes(pcm.tobytes())
 
+    torch.save(vsd, str(tmp_path / "pytorch_model.bin"))  # the released Vocos checkpoint's file name
+    with pytest.raises(FileNotFoundError):  # no weights and no network: refuse to vocode with random parameters
+        f5b200.load_vocoder("vocos", is_local=False, local_path="", device="cuda")
     tts = A.F5TTS(model=str(tmp_path / "tiny.yaml"), ckpt_file=str(tmp_path / "model.safetensors"),
-                  vocab_file=str(tmp_path / "vocab.txt"), device="cuda",
+                  vocab_file=str(tmp_path / "vocab.txt"), device="cuda", vocoder_local_path=str(tmp_path),
                   tokenize=f5b200.tokenizers.char_tokens)  # plain character vocabulary: explicit opt-in
-    tts.vocoder.load_state_dict(vsd)
+    assert tts.vocoder.precision == "bf16"  # 16-bit kernels by default on CUDA, like the backbone
     tts.ema_model.transformer.float()
     tts.vocoder.precision = "fp32"
     ref_text = "a bc."

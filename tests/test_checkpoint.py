@@ -88,6 +88,42 @@ def test_load_checkpoint_formats_cpu(tmp_path, fmt, use_ema):
     assert model.transformer.precision == "fp32"
 
 
+@pytest.mark.parametrize("with_inv_freq", [True, False])
+def test_reference_checkpoints_carry_rotary_inv_freq(tmp_path, with_inv_freq):
+    """trainer-written checkpoints hold `transformer.rotary_embed.inv_freq` (x_transformers registers
+    it as a persistent buffer); a strict load must accept it -- and still accept a file written without it."""
+    cfg, state = _plain_state()
+    ema = {"ema_model." + k: v for k, v in state.items()}
+    if with_inv_freq:
+        ema["ema_model.transformer.rotary_embed.inv_freq"] = 1.0 / (10000.0 ** (torch.arange(0, 64, 2).float() / 64))
+    ema.update(initted=torch.tensor(True), step=torch.tensor(7))
+    path = str(tmp_path / "model.pt")
+    torch.save({"ema_model_state_dict": ema}, path)
+    model = f5b200.CFM(transformer=f5b200.DiT(**CFG, text_num_embeds=len(VOCAB) + 1, mel_dim=100),
+                       mel_spec_kwargs=dict(mel_spec_type="vocos"))
+    model = CK.load_checkpoint(model, path, "cpu", use_ema=True)
+    assert "transformer.rotary_embed.inv_freq" in model.state_dict()
+
+
+def test_live_reference_state_dict_loads_strictly(tmp_path):
+    """The state dict of the reference's own CFM(DiT) (unmodified modules through the loader) loads strictly."""
+    from oracle import make_golden, ref_loader
+
+    if not ref_loader.available():
+        pytest.skip("/root/reference is only present in the build container")
+    R = ref_loader.load()
+    cfg, state = _plain_state()
+    ref = make_golden.build_reference(R, cfg, {k[len("transformer."):]: v for k, v in state.items()})
+    sd = {k: v for k, v in ref.state_dict().items() if not k.startswith("mel_spec.")}
+    assert "transformer.rotary_embed.inv_freq" in sd
+    torch.save({"model_state_dict": sd}, str(tmp_path / "ref.pt"))
+    model = f5b200.CFM(transformer=f5b200.DiT(**CFG, text_num_embeds=len(VOCAB) + 1, mel_dim=100),
+                       mel_spec_kwargs=dict(mel_spec_type="vocos"))
+    CK.load_checkpoint(model, str(tmp_path / "ref.pt"), "cpu", use_ema=False)
+    for k, v in sd.items():
+        assert torch.equal(model.state_dict()[k], v), k
+
+
 def test_load_checkpoint_is_strict(tmp_path):
     _, state = _plain_state()
     state.pop(next(iter(state)))

@@ -170,3 +170,20 @@ def test_missing_weight_is_loud():
     m = f5b200.DiT(dim=128, depth=1, heads=2, ff_mult=2, text_dim=64, conv_layers=1, text_num_embeds=10, precision="fp32")
     with pytest.raises(f5b200.F5BError):
         m(torch.zeros(1, 8, 100), torch.zeros(1, 8, 100), torch.zeros(1, 3, dtype=torch.long), torch.tensor(0.5))
+
+
+def test_text_id_out_of_range_raises_index_error():
+    """nn.Embedding raises IndexError on an id outside the table (dit.py:42,94); the device lookup must not read out of
+    bounds silently: the call fails with IndexError, and the next valid call works."""
+    cfg = O.ArchCfg(dim=128, depth=1, heads=2, ff_mult=2, text_dim=64, conv_layers=1, text_num_embeds=10)
+    sd = O.synth_backbone_weights(cfg, seed=1)
+    cfm = build_cfm(cfg, sd, "fp32")
+    cond, text = O.synth_inputs(40, 12, 6, vocab=10, seed=2)
+    good, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), duration=40, steps=2, cfg_strength=2.0, seed=1)
+    for bad_id in (10, 4000, -2):  # valid ids are -1 (padding) .. text_num_embeds - 1
+        bad = text.clone()
+        bad[0, 2] = bad_id
+        with pytest.raises(IndexError):
+            cfm.sample(cond=cond.cuda(), text=bad.cuda(), duration=40, steps=2, cfg_strength=2.0, seed=1)
+    again, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), duration=40, steps=2, cfg_strength=2.0, seed=1)
+    assert torch.equal(good, again)

@@ -31,6 +31,8 @@ def test_state_dict_names_and_shapes(name):
             text_mask_padding=cfg.text_mask_padding)
     want = O.backbone_param_shapes(cfg)  # pinned against the reference modules by oracle/make_golden.py (strict load)
     got = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    # x_transformers' RotaryEmbedding keeps inv_freq as a persistent buffer: reference checkpoints carry this key
+    assert got.pop("rotary_embed.inv_freq") == (32,)
     assert got == {k: tuple(v) for k, v in want.items()}
     if cfg.backbone == "DiT":  # reference zero-initialisation (dit.py:214-224, modules.py:234-235)
         sd = m.state_dict()

@@ -34,6 +34,7 @@ import torch  # noqa: E402
 MODEL = "F5TTS_v1_Base"
 N_TOTAL, N_REF, N_TEXT, NFE, CFG, SWAY = 940, 282, 170, 16, 2.0, -1.0
 GEN_FRAMES = N_TOTAL - N_REF  # 658 generated frames = 7.02 s at 24 kHz / hop 256
+GOLDEN_SEEDS = (0, 1)  # inputs cycle over these; tests/golden/c2_oracle_seed{s}.npz holds the fp32 oracle's mel for each
 HOP, SR = 256, 24000
 METRIC, UNIT = "generated_mel_frames_per_sec", "frames/s"
 DTYPE_DETAIL = ("16-bit tensor-core mode: tcgen05 kind::f16, fp32 accumulate; attention q/k/v/P bf16, linear-layer "
@@ -96,6 +97,15 @@ V1_BASE = dict(dim=1024, depth=22, heads=16, ff_mult=2, text_dim=512, text_mask_
                pe_attn_head=None, text_num_embeds=59)  # configs/F5TTS_v1_Base.yaml:24-37; vocab 58 (+1, utils_infer.py:315)
 
 
+def _rerandomise(dit, seed: int):
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in dit.named_parameters():
+            if "attn_norm.linear" in name or name.startswith("norm_out.") or name.startswith("proj_out.") or ".grn." in name:
+                p.copy_(torch.randn(p.shape, generator=g) * 0.02)
+    return g
+
+
 def synth_state(seed: int = 0):
     """Reference-constructor initialisation, then the zero-initialised parameters (AdaLN linears, proj_out, GRN:
     dit.py:214-224, modules.py:234-235) are re-drawn N(0, 0.02^2) so the velocity field is non-trivial."""
@@ -103,11 +113,7 @@ def synth_state(seed: int = 0):
 
     torch.manual_seed(seed)
     dit = f5b200.DiT(**V1_BASE, precision="bf16")
-    g = torch.Generator().manual_seed(seed + 1)
-    with torch.no_grad():
-        for name, p in dit.named_parameters():
-            if "attn_norm.linear" in name or name.startswith("norm_out.") or name.startswith("proj_out.") or ".grn." in name:
-                p.copy_(torch.randn(p.shape, generator=g) * 0.02)
+    g = _rerandomise(dit, seed + 1)
     voc = f5b200.Vocos(precision="bf16")
     with torch.no_grad():
         for name, p in voc.named_parameters():
@@ -120,15 +126,15 @@ def synth_state(seed: int = 0):
     return dit, voc
 
 
-def synth_inputs(seed: int):
+def synth_inputs(seed: int, n_total: int = N_TOTAL, n_ref: int = N_REF, n_text: int = N_TEXT):
     """Log-mel-like prompt (mean -3, std 2, clamp >= ln 1e-5), uniform token ids, seeded noise (cfm.py:196-201)."""
     import math
 
     g = torch.Generator().manual_seed(1000 + seed)
-    cond = (torch.randn(1, N_REF, 100, generator=g) * 2.0 - 3.0).clamp(min=math.log(1e-5))
-    text = torch.randint(0, 58, (1, N_TEXT), generator=g)
+    cond = (torch.randn(1, n_ref, 100, generator=g) * 2.0 - 3.0).clamp(min=math.log(1e-5))
+    text = torch.randint(0, 58, (1, n_text), generator=g)
     torch.manual_seed(seed)
-    y0 = torch.randn(N_TOTAL, 100).unsqueeze(0)
+    y0 = torch.randn(n_total, 100).unsqueeze(0)
     return cond, text, y0
 
 
@@ -184,66 +190,103 @@ def roofline_gemm(stream, pk) -> dict:
                                       "note": "operands are L2-resident at batch 1 (11.5 MB): latency-, not HBM-bound"}}}
 
 
-# ---- CPU leg: the oracle port of the reference path on the host cores (the only place oracle/ is executed) --------
-def cpu_reference_sample(state, vstate, seed: int, threads: int):
-    """One bounded sample of the workload on the CPU: ONE of the NFE=16 CFG-doubled DiT evaluations (N=940) plus the
-    full Vocos decode of 658 frames; the utterance time is extrapolated as 16 x eval + vocos (stated in `sample`)."""
+# ---- CPU legs: the oracle port of the reference path on the host cores (the only place oracle/ is executed) ----------
+def cpu_model_name() -> str:
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def cpu_reference_utterance(state, vstate, seed: int, threads: int, model: str = MODEL, n_total: int = N_TOTAL,
+                            n_ref: int = N_REF, n_text: int = N_TEXT):
+    """One WHOLE utterance on the CPU, nothing extrapolated: `CFM.sample` (all NFE CFG-doubled evaluations + Euler,
+    oracle/f5_oracle.py:cfm_sample) and the Vocos decode of the mel it produced.  Returns (sample_s, vocos_s, mel)."""
     from oracle import f5_oracle as O  # checker / CPU baseline only
 
     torch.set_num_threads(threads)
-    cfg = O.ArchCfg.named(MODEL)
-    cond, text, y0 = synth_inputs(seed)
-    cond_p, text_i, dur, cond_mask, step_cond, mask = O.prepare_sample(cond, text, N_TOTAL, None)
-    t = O.time_grid(NFE, SWAY)
+    cfg = O.ArchCfg.named(model)
+    cond, text, y0 = synth_inputs(seed, n_total, n_ref, n_text)
     with torch.no_grad():
         t0 = time.perf_counter()
-        O.backbone_forward(state, cfg, y0, step_cond, text_i, t[3], mask, cfg_infer=True, cache=O.TextCache())
-        t_eval = time.perf_counter() - t0
-        mel = (torch.randn(1, 100, GEN_FRAMES) * 2.0 - 3.0).clamp(min=-11.5)
+        ref = O.cfm_sample(state, cfg, cond, text, n_total, steps=NFE, cfg_strength=CFG, sway_sampling_coef=SWAY, y0=y0)
+        t_sample = time.perf_counter() - t0
+        mel = ref.out[:, n_ref:, :].permute(0, 2, 1).contiguous()
         t0 = time.perf_counter()
         O.vocos_decode(vstate, mel)
         t_voc = time.perf_counter() - t0
-    return t_eval, t_voc
+    return t_sample, t_voc, ref.out
 
 
-def cpu_line(state, vstate, threads: int, repeats: int = 1):
-    best = None
-    for r in range(repeats):
-        te, tv = cpu_reference_sample(state, vstate, r, threads)
-        tot = NFE * te + tv
-        best = tot if best is None else min(best, tot)
-    return {"value": round(GEN_FRAMES / best, 3), "unit": UNIT, "cores": threads, "kind": "port",
-            "rtf": round(best / (GEN_FRAMES * HOP / SR), 4),
-            "sample": f"1 of {NFE} CFG-doubled DiT evaluations (N={N_TOTAL}, fp32, oracle/f5_oracle.py) + full Vocos "
-                      f"decode of {GEN_FRAMES} frames; utterance time extrapolated as {NFE} x eval + vocos"}
+def cpu_line(state, vstate, threads: int):
+    """cpu_baseline of our own line: ONE full C2 utterance (about 15-30 s on the box's cores), measured, not scaled."""
+    ts, tv, _ = cpu_reference_utterance(state, vstate, GOLDEN_SEEDS[0], threads)
+    tot = ts + tv
+    return {"value": round(GEN_FRAMES / tot, 3), "unit": UNIT, "cores": threads, "cpu_model": cpu_model_name(),
+            "kind": "port", "rtf": round(tot / (GEN_FRAMES * HOP / SR), 4),
+            "sample_s": round(ts, 3), "vocos_s": round(tv, 3),
+            "sample": f"1 whole C2 utterance: CFM.sample with all {NFE} CFG-doubled DiT evaluations (N={N_TOTAL}, fp32, "
+                      f"oracle/f5_oracle.py) + Vocos decode of the sampled {GEN_FRAMES} frames; nothing extrapolated"}
+
+
+def cpu_c1(threads: int):
+    """BASELINE.json configs[0] in full (the reference's own CPU-runnable case): F5TTS_Small, one utterance of N = 750
+    frames (282 prompt + 468 generated = 4.99 s), NFE 16 + sway, CFG 2.0, Vocos.  One run, no warm-up (stated)."""
+    import f5b200
+
+    torch.manual_seed(0)
+    small = f5b200.DiT(dim=768, depth=18, heads=12, ff_mult=2, text_dim=512, text_mask_padding=False, conv_layers=4,
+                       pe_attn_head=1, text_num_embeds=59, precision="fp32")
+    _rerandomise(small, 1)
+    _, voc = synth_state(0)
+    state = {k: v.detach().float() for k, v in small.state_dict().items()}
+    vstate = {k: v.detach().float() for k, v in voc.state_dict().items()}
+    n_total, n_ref = 750, 282
+    ts, tv, _ = cpu_reference_utterance(state, vstate, 0, threads, "F5TTS_Small", n_total, n_ref, 135)
+    gen_s = (n_total - n_ref) * HOP / SR
+    return {"workload": "C1: F5TTS_Small random-init, 1 utterance N=750 (282 prompt + 468 generated = 4.99 s), NFE 16 + "
+                        "sway -1, CFG 2.0, Vocos, CPU fp32 oracle port; one run, no warm-up",
+            "sample_s": round(ts, 3), "vocos_s": round(tv, 3), "rtf": round((ts + tv) / gen_s, 4),
+            "generated_mel_frames_per_sec": round((n_total - n_ref) / (ts + tv), 3), "cores": threads}
 
 
 def run_reference(args, rank: int, world: int):
-    """--impl reference: the reference's CPU implementation of the path (oracle port: /root/reference does not exist on
-    the GPU box and its third-party deps are absent) on all host threads; rank 0 only."""
+    """--impl reference: the reference's CPU implementation of the path on all host threads; rank 0 only.  It is the
+    oracle PORT (`kind: "port"`): the reference's own modules need /root/reference (absent on the GPU box) and
+    third-party packages that are not in the image (torchdiffeq, x_transformers, vocos).  Every step is a
+    WHOLE utterance -- all 16 evaluations and the Vocos decode of the sampled mel -- so the line is a measurement."""
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     dit, voc = synth_state(0)
     state = {k: v.detach().float() for k, v in dit.state_dict().items()}
     vstate = {k: v.detach().float() for k, v in voc.state_dict().items()}
-    for _ in range(min(args.warmup, 1)):
-        cpu_reference_sample(state, vstate, 99, threads)
-    tot = 0.0
-    for s in range(args.steps):
-        te, tv = cpu_reference_sample(state, vstate, s, threads)
-        tot += NFE * te + tv
-    per = tot / args.steps
+    for i in range(min(args.warmup, 1)):
+        cpu_reference_utterance(state, vstate, GOLDEN_SEEDS[0], threads)
+    t_s = t_v = 0.0
+    for i in range(args.steps):
+        ts, tv, _ = cpu_reference_utterance(state, vstate, GOLDEN_SEEDS[i % len(GOLDEN_SEEDS)], threads)
+        t_s += ts
+        t_v += tv
+    per = (t_s + t_v) / args.steps
     val = GEN_FRAMES / per
+    sample = (f"per step: 1 whole C2 utterance = CFM.sample with all {NFE} CFG-doubled DiT evaluations + Vocos decode of "
+              f"the sampled mel, fp32, {threads} threads; measured, nothing extrapolated")
     line = {"metric": METRIC, "value": round(val, 3), "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(per * 1e3, 2), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "rtf": round(per / (GEN_FRAMES * HOP / SR), 4),
+            "sample_s_per_step": round(t_s / args.steps, 3), "vocos_s_per_step": round(t_v / args.steps, 3),
             "config": workload_config(1),
-            "cpu_baseline": {"value": round(val, 3), "unit": UNIT, "cores": threads, "kind": "port",
-                             "sample": f"per step: 1 of {NFE} CFG-doubled DiT evaluations + full Vocos decode, "
-                                       f"utterance time = {NFE} x eval + vocos"},
+            "cpu_baseline": {"value": round(val, 3), "unit": UNIT, "cores": threads, "cpu_model": cpu_model_name(),
+                             "kind": "port", "sample": sample},
             "e2e": {"value": round(val, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if not args.no_c1:
+        line["c1"] = cpu_c1(threads)
     print(json.dumps(line), flush=True)
 
 
@@ -256,6 +299,22 @@ def workload_config(world: int) -> dict:
 
 
 # ---- our arm -------------------------------------------------------------------------------------------------------
+MEL_TOL_16BIT = 2e-2  # north star: 16-bit mode mel within 2e-2 max-abs of the fp32 reference
+
+
+def check_against_oracle(mel: torch.Tensor, seed: int) -> dict:
+    """The mel of the LAST TIMED utterance against the committed fp32-oracle output of the same utterance
+    (tests/golden/c2_oracle_seed{seed}.npz, oracle/make_golden_c2.py).  A timed run that is fast and wrong fails here."""
+    import numpy as np
+
+    path = os.path.join(ROOT, "tests", "golden", f"c2_oracle_seed{seed}.npz")
+    want = torch.from_numpy(np.load(path)["mel"])
+    err = float((mel[0].detach().float().cpu() - want).abs().max())
+    assert err <= MEL_TOL_16BIT, f"timed output differs from the fp32 oracle: max-abs {err:.3e} > {MEL_TOL_16BIT}"
+    return {"mel_max_abs_vs_fp32_oracle": round(err, 6), "tol": MEL_TOL_16BIT, "utterance_seed": seed,
+            "golden": os.path.relpath(path, ROOT), "mel_abs_max": round(float(want.abs().max()), 3)}
+
+
 def run_ours(args, rank: int, world: int, local_rank: int):
     import torch.distributed as dist
 
@@ -286,13 +345,18 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         return float(t.item())
 
     n_in = args.warmup + args.steps
-    host_in = [synth_inputs(rank * 100003 + i) for i in range(n_in)]
+    # inputs cycle over GOLDEN_SEEDS (offset by rank): every timed utterance has a committed fp32-oracle result
+    seed_of = lambda i: GOLDEN_SEEDS[(i + rank) % len(GOLDEN_SEEDS)]  # noqa: E731
+    host_in = [synth_inputs(seed_of(i)) for i in range(n_in)]
     dev_in = [tuple(t.to(dev) for t in x) for x in host_in]
     pin_in = [tuple(t.pin_memory() for t in x) for x in host_in]
+
+    last = {}
 
     def step_device(i):
         cond, text, y0 = dev_in[i]
         mel, _ = cfm.sample(cond=cond, text=text, y0=y0, **kw)
+        last["mel"], last["seed"] = mel, seed_of(i)
         return voc.decode(mel[:, N_REF:, :].permute(0, 2, 1).contiguous())
 
     def step_e2e(i):
@@ -320,6 +384,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         clocks = clk.stop()
         ms_total = reduce_max(e0.elapsed_time(e1))
         assert torch.isfinite(wav).all(), "non-finite waveform"
+        check = check_against_oracle(last["mel"], last["seed"])
         # -------- e2e: public API, host tensors in, waveform out (wall clock, synchronised both sides) --------
         for i in range(min(args.warmup, 2)):
             step_e2e(i)
@@ -347,7 +412,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
             "config": workload_config(world),
             "rtf": round(ms_step / 1e3 / gen_s, 5), "rtf_e2e": round(e2e_s / args.steps / gen_s, 5),
             "e2e": {"value": round(e2e_val, 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-            "gpu_launches": int(launches), "clocks": clocks,
+            "gpu_launches": int(launches), "clocks": clocks, "check": check,
             "step_tflops": {"achieved": round(step_tf, 1), "peak_sustained": pk["tf_sus"],
                             "frac": round(step_tf / pk["tf_sus"], 4),
                             "flops_per_step": NFE * flops_per_eval() + 27.0e6 * GEN_FRAMES},
@@ -366,6 +431,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-c1", action="store_true", help="reference arm: skip the C1 (F5TTS_Small) CPU run")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

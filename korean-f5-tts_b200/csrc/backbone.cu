@@ -343,6 +343,8 @@ void f5b_plan::ensure_ws(int B, int N, int nt, int steps, bool want_traj) {
     bf.cat = A.alloc((size_t)rows * 2 * d * es);
     for (int i = 0; i < a.depth / 2; ++i) bf.skips.push_back(A.alloc_n<float>((size_t)rows * d));
   }
+  this->bf = nb;  // commit: every allocation succeeded
+  wk = std::move(fresh);
 }
 
 // ---------------------------------------------------------------------------------------------

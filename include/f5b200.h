@@ -128,7 +128,7 @@ int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int3
  *          2 = LN+modulate (M rows, N = dim). */
 int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, float* ms, int32_t device, void* stream);
 
-/* Debug timeline of one attention CTA (clock64 stamps, see csrc/runtime.cu); out = int64[3*64*4]. */
+/* Debug timeline of one attention CTA (clock64 stamps, see csrc/runtime.cu); out = int64[3*64*8]. */
 int f5b_debug_attn_trace(int32_t rows, int32_t heads, int32_t batches, int64_t* out, int32_t device);
 
 /* Debug in-situ kernel timeline (library built with F5B_KTRACE=1 only; otherwise F5B_ERR_INVALID).

@@ -1,6 +1,7 @@
 // Runtime plumbing: errors, arena, weight store, contraction dispatch, kernel-level C entry points.
 #include <atomic>
 #include <cstdlib>
+#include <cmath>
 #include <cstring>
 
 #include "plan.h"
@@ -75,6 +76,34 @@ __global__ void pad_convert_kernel(const float* __restrict__ in, T* __restrict__
   long long r = i / ld;
   int c = (int)(i - r * ld);
   st_from_float(out + i, c < K ? in[r * K + c] : 0.0f);
+}
+
+// Pseudo-random 16-bit operands for the kernel timers (f5b_op_time): constant data toggles few bits, and tensor-core
+// power -- on a power-capped part, the clock -- depends on the data.  Uniform in [-amp, amp), hash of the index.
+__global__ void fill_random16_kernel(uint16_t* __restrict__ out, long long n, float amp, uint32_t seed, int fp16) {
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  uint32_t h = (uint32_t)i * 2654435761u ^ seed;
+  h ^= h >> 16; h *= 0x7feb352du; h ^= h >> 15; h *= 0x846ca68bu; h ^= h >> 16;
+  const float v = ((h >> 8) * (1.0f / 8388608.0f) - 1.0f) * amp;
+  if (fp16) {
+    __half x = __float2half_rn(v);
+    out[i] = *reinterpret_cast<uint16_t*>(&x);
+  } else {
+    bf16 x = __float2bfloat16_rn(v);
+    out[i] = *reinterpret_cast<uint16_t*>(&x);
+  }
+}
+static void fill_random16(cudaStream_t st, void* p, long long n, float amp, uint32_t seed, int fp16 = 0) {
+  fill_random16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(reinterpret_cast<uint16_t*>(p), n, amp, seed, fp16);
+  F5B_POST_LAUNCH();
+}
+__global__ void fill_random32_kernel(float* __restrict__ out, long long n, float amp, uint32_t seed) {
+  long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  uint32_t h = (uint32_t)i * 2654435761u ^ seed;
+  h ^= h >> 16; h *= 0x7feb352du; h ^= h >> 15; h *= 0x846ca68bu; h ^= h >> 16;
+  out[i] = ((h >> 8) * (1.0f / 8388608.0f) - 1.0f) * amp;
 }
 
 __global__ void widen_kernel(const bf16* __restrict__ in, float* __restrict__ o, long long n) {
@@ -295,7 +324,7 @@ int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int3
 }
 
 
-/* Debug: run the tcgen05 attention once on constant data with the in-kernel timeline enabled; out[3][64][4] receives
+/* Debug: run the tcgen05 attention once on constant data with the in-kernel timeline enabled; out[3][64][8] receives
  * clock64 stamps of CTA (0,0,0): who 0/1 = softmax tile 0/1 {wait S, S ready, max done, P handed over}, who 2 = MMA
  * issuer {wait P0, P0 seen, wait P1, P1 seen} per key block. */
 int f5b_debug_attn_trace(int32_t rows, int32_t heads, int32_t batches, int64_t* out, int32_t device) {
@@ -404,8 +433,8 @@ int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, f
     if (ncopy > iters) ncopy = iters;
     bf16* W = arena.alloc_n<bf16>((size_t)N * ld * ncopy);
     bf16* O = arena.alloc_n<bf16>((size_t)M * N);
-    F5B_CHECK_CUDA(cudaMemsetAsync(A, 0x3c, (size_t)M * ld * 2, st));
-    F5B_CHECK_CUDA(cudaMemsetAsync(W, 0x3c, wbytes * ncopy, st));
+    fill_random16(st, A, (long long)M * ld, 1.0f, 1u);                          // LN-like activations
+    fill_random16(st, W, (long long)N * ld * ncopy, 1.7f / sqrtf((float)K), 2u);  // std ~ 1 / sqrt(K)
     EpiParams ep;
     ep.out = O;
     ep.out_type = 1;
@@ -429,14 +458,16 @@ int f5b_op_time(int32_t which, int32_t M, int32_t N, int32_t K, int32_t iters, f
     const int rows = M, heads = N, batches = K, inner = heads * 64;
     bf16* Q = arena.alloc_n<bf16>((size_t)batches * rows * 3 * inner);
     bf16* O = arena.alloc_n<bf16>((size_t)batches * rows * inner);
-    F5B_CHECK_CUDA(cudaMemsetAsync(Q, 0x3c, (size_t)batches * rows * 3 * inner * 2, st));
+    fill_random16(st, Q, (long long)batches * rows * 3 * inner, 1.7f, 3u);  // unit-variance q, k, v: scores ~ N(0, 1)
     timed([&] { tc_attention(st, Q, O, batches, rows, heads, nullptr, 0.125f); });
   } else if (which == 2) {
     float* X = arena.alloc_n<float>((size_t)M * N);
     bf16* O = arena.alloc_n<bf16>((size_t)M * N);
     float* V = arena.alloc_n<float>((size_t)2 * N);
-    F5B_CHECK_CUDA(cudaMemsetAsync(X, 0x3c, (size_t)M * N * 4, st));
-    F5B_CHECK_CUDA(cudaMemsetAsync(V, 0, (size_t)2 * N * 4, st));
+    fill_random32_kernel<<<(unsigned)(((long long)M * N + 255) / 256), 256, 0, st>>>(X, (long long)M * N, 1.7f, 4u);
+    F5B_POST_LAUNCH();
+    fill_random32_kernel<<<(unsigned)((2 * N + 255) / 256), 256, 0, st>>>(V, 2 * N, 0.1f, 5u);
+    F5B_POST_LAUNCH();
     timed([&] { ln_mod<bf16>(st, X, O, M, N, V, V + N, 1.0f, 0, 1 << 30, 1, 1e-6f); });
   } else {
     F5B_REQUIRE(false, "unknown kernel selector");

@@ -190,7 +190,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 0 && lane == 0) {
+  // Single-lane roles are entered through elect.sync, not a lane test: the compiler then knows exactly one lane is active
+  // and feeds tcgen05.mma / cp.async.bulk.tensor straight from uniform registers.  Behind `lane == 0` it wraps EVERY such
+  // instruction in a loop over the possibly-active lanes (ELECT / R2UR / BRA.U.ANY): 257 of those loops in this file
+  // before the change, ~70 cycles of issue per MMA against a 64-cycle tensor floor at BN = 128.
+  const bool lead_warp0 = warp == 0, lead_warp1 = warp == 1 && rank == 0;
+  if (lead_warp0 && elect_one()) {
     // ------------------------------- TMA producer -------------------------------
     // The weights do not depend on the previous kernel: the W tiles of the first ring fill are requested BEFORE the
     // programmatic-dependency wait, so their HBM latency overlaps the predecessor's tail; the A tiles follow after it.
@@ -239,7 +244,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
     }
-  } else if (warp == 1 && lane == 0 && rank == 0) {
+  } else if (lead_warp1 && elect_one()) {
     // ------------------------------- MMA issuer ---------------------------------
     // Descriptors are built once: only the 14-bit start-address field (bytes >> 4) changes between MMAs, and it cannot
     // carry out of its field (smem addresses < 256 KB), so a stage / k-step advance is a plain add.  The issuing thread
@@ -287,7 +292,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are this warp's
     const int rl = quarter * 32 + lane;  // row inside the tile
     const int grp = (warp - 2) >> 2;  // units of 64 columns alternate between the two groups
-    const bool issuer = ((warp - 2) & 3) == 0 && lane == 0;
+    const bool issuer_warp = ((warp - 2) & 3) == 0;  // its elected lane (deterministic for a full mask) issues the bulk stores
+    const bool issuer = issuer_warp && lane == 0;      // trace stamps only
     uint8_t* sOg = sO + grp * EPI_NBUF * EPI_BUF_BYTES;
     constexpr bool GEN = VAR == EV_GENERIC;
     constexpr bool MAY_ROPE = GEN || VAR == EV_STORE16;
@@ -401,10 +407,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
           // two staging buffers per group: the store issued at the previous flush has to be done reading its buffer
           // before anyone passes this barrier and starts to fill it again (it had a whole chunk of time to do so)
-          if (issuer && !dry) bulk_wait_read<0>();
+          if (issuer_warp && !dry && elect_one()) bulk_wait_read<0>();
           named_bar_sync(1 + grp, 128);
           if (dry) break;
-          if (issuer && r0 < s.rows_per_batch) {
+          if (issuer_warp && r0 < s.rows_per_batch && elect_one()) {
             if (resid) tma_reduce_add_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             else tma_store_3d(&tmO, buf, c_first, r0 - ep.row_skip, bz);
             bulk_commit();
@@ -427,7 +433,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     if (issuer && grp == 0) KT_MARK(5);  // last store issued
     // the staging buffers must outlive the reads of the bulk stores; the writes themselves complete with the grid
-    if (issuer) bulk_wait_read<0>();
+    if (issuer_warp && elect_one()) bulk_wait_read<0>();
   }
 
   tc_fence_before();

@@ -60,7 +60,7 @@ void ktrace_set_tc_gemm(unsigned long long* p);  // per-translation-unit trace p
 void ktrace_set_tc_attn(unsigned long long* p);
 void ktrace_set_rowwise(unsigned long long* p);
 void attn_trace_enable(int on);
-void attn_trace_read(long long* host /* [3][64][4] clock64 stamps */);
+void attn_trace_read(long long* host /* [3][64][8] clock64 stamps */);
 void tc_init_kernels();       // attention
 void tc_gemm_init_kernels();  // GEMM
 void simt_init_kernels();

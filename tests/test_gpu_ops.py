@@ -110,6 +110,25 @@ def test_attention_bf16_tcgen05(batches, rows, heads, lens):
     assert err <= 2e-2, f"max err {err}"  # P and the output are rounded to bf16
 
 
+@pytest.mark.parametrize("rows,heads", [(700, 2), (1300, 1)])
+def test_attention_bf16_rising_scores_rescale_path(rows, heads):
+    """Keys whose scores keep growing along the sequence: every later key block raises the row maximum by far more
+    than the lazy-rescaling threshold (2^8), so the O / row-sum rescale in tensor memory is exercised in every block."""
+    g = torch.Generator().manual_seed(rows)
+    qkv = torch.randn(rows, 3 * heads * 64, generator=g)
+    inner = heads * 64
+    q = qkv[:, :inner].view(rows, heads, 64)
+    k = qkv[:, inner:2 * inner].view(rows, heads, 64)
+    # align k with the mean query direction and let its length grow with the position: scores rise by ~60 per block
+    d = torch.nn.functional.normalize(q.mean(0), dim=-1)
+    q += 3.0 * d[None]
+    k += (torch.arange(rows)[:, None, None] / 128.0) * 20.0 * d[None]
+    out = _attention(1, qkv, None, 1, rows, heads)
+    ref = _attention_ref(qkv.bfloat16().float(), None, 1, rows, heads)
+    err = (out - ref).abs().max()
+    assert torch.isfinite(out).all() and err <= 3e-2, f"max err {err}"
+
+
 def test_op_time_runs():
     L = _lib()
     ms = C.c_float()

@@ -298,6 +298,143 @@ def workload_config(world: int) -> dict:
             "l2": "per-step working set (0.66 GB bf16 weights streamed every function evaluation) exceeds the 126 MB L2"}
 
 
+# ---- C3: the multi-GPU configuration north_star names (BASELINE.json configs[2]) -------------------------------------
+C3_UTTERANCES, C3_NFE, C3_MAX_ROWS = 256, 32, 16384
+
+
+def c3_lengths():
+    """256 utterances, total seconds ~ U(3, 20) with seed 0, prompt = first 3 s."""
+    g = torch.Generator().manual_seed(0)
+    secs = torch.rand(C3_UTTERANCES, generator=g) * 17.0 + 3.0
+    return [int(x * SR) // HOP + 1 for x in secs.tolist()], 3 * SR // HOP + 1
+
+
+def run_c3(cfm, voc, dev, stream, rank: int, world: int, pk: dict) -> dict:
+    """STRONG scaling of one fixed job: 256 variable-length utterances (padded masks, attn_mask_enabled), NFE 32, CFG
+    2.0, Vocos; the request list is sharded over the ranks by an attention-aware LPT rule (f5b200/sharding.py; the
+    reference shards its request list with accelerate's split_between_processes, eval/eval_infer_batch.py:181) and each
+    rank runs its shard as length-sorted micro-batches -- no collective on the data path.  Reported: the job's device
+    time = max over ranks, per-rank times and their imbalance, aggregate generated-audio seconds per second."""
+    import torch.distributed as dist
+
+    from f5b200.sharding import micro_batches, my_shard
+
+    frames, n_ref = c3_lengths()
+    mine = my_shard(frames, rank, world)
+    groups = micro_batches(mine, frames, max_rows=C3_MAX_ROWS, max_batch=64)
+
+    def inputs(grp):
+        b, n = len(grp), max(frames[i] for i in grp)
+        gg = torch.Generator().manual_seed(17 + grp[0])
+        cond = (torch.randn(b, n_ref, 100, generator=gg) * 2.0 - 3.0).clamp(min=-11.5)
+        nt = max(int(0.18 * n), 8)
+        text = torch.randint(0, 58, (b, nt), generator=gg)
+        for r, i in enumerate(grp):
+            text[r, int(0.18 * frames[i]):] = -1
+        dur = torch.tensor([frames[i] for i in grp])
+        y0 = torch.randn(b, n, 100, generator=gg)
+        glen = torch.tensor([frames[i] - n_ref for i in grp], dtype=torch.int32)
+        return cond.to(dev), text.to(dev), dur.to(dev), y0.to(dev), glen.to(dev)
+
+    def run(grp, data):
+        cond, text, dur, y0, glen = data
+        b = len(grp)
+        mel, _ = cfm.sample(cond=cond, text=text, duration=dur if b > 1 else int(dur[0]), steps=C3_NFE, cfg_strength=CFG,
+                            sway_sampling_coef=SWAY, y0=y0, return_trajectory=False)
+        return voc.decode(mel[:, n_ref:, :].permute(0, 2, 1).contiguous(), glen if b > 1 else None)
+
+    data = [inputs(grp) for grp in groups]
+    with torch.cuda.stream(stream):
+        run(groups[-1], data[-1])  # warm-up: the smallest and the largest micro-batch (workspace growth, module load)
+        run(groups[0], data[0])
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for grp, d in zip(groups, data):
+            wav = run(grp, d)
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        assert torch.isfinite(wav).all()
+    t_mine = e0.elapsed_time(e1) / 1e3
+    gen_mine = sum(frames[i] - n_ref for i in mine)
+    padded = sum(len(grp) * max(frames[i] for i in grp) for grp in groups)
+    stats = torch.tensor([t_mine, float(gen_mine), float(len(mine)), float(len(groups)), float(padded),
+                          float(sum(frames[i] for i in mine))], dtype=torch.float64, device=dev)
+    if world > 1:
+        allst = [torch.zeros_like(stats) for _ in range(world)]
+        dist.all_gather(allst, stats)
+    else:
+        allst = [stats]
+    allst = torch.stack(allst).cpu()
+    t_all = allst[:, 0].tolist()
+    t_job = max(t_all)
+    gen_total = float(allst[:, 1].sum())
+    flops = sum(flops_per_eval(n=f) for f in frames) * C3_NFE
+    return {"workload": f"C3: {MODEL}, {C3_UTTERANCES} utterances of 3-20 s ({sum(frames)} frames, prompt {n_ref}), NFE "
+                        f"{C3_NFE}, CFG {CFG} doubled batch, key masks on, Vocos; request-sharded x{world} (LPT), "
+                        f"micro-batches <= {C3_MAX_ROWS} padded frames, eager launches",
+            "scaling": "strong", "device_s": round(t_job, 4), "per_rank_device_s": [round(x, 4) for x in t_all],
+            "imbalance_max_over_mean": round(t_job / (sum(t_all) / len(t_all)), 4),
+            "utterances_per_rank": [int(x) for x in allst[:, 2].tolist()],
+            "micro_batches_per_rank": [int(x) for x in allst[:, 3].tolist()],
+            "padding_overhead": round(float(allst[:, 4].sum() / allst[:, 5].sum()) - 1.0, 4),
+            "generated_audio_s_per_s": round(gen_total * HOP / SR / t_job, 2),
+            "generated_frames_per_s": round(gen_total / t_job, 1),
+            "rtf": round(t_job / (gen_total * HOP / SR), 6),
+            "tflops_unpadded_per_gpu": round(flops / t_job / world / 1e12, 1),
+            "frac_of_sustained_peak": round(flops / t_job / world / 1e12 / pk["tf_sus"], 4)}
+
+
+# ---- C4: E2TTS_Base flat-UNet transformer, ~30 s (BASELINE.json configs[3]) ------------------------------------------
+C4_N, C4_NTEXT, C4_NFE = 2800, 500, 32
+
+
+def flops_per_eval_unett(dim=1024, depth=24, heads=16, ff_mult=4, n=C4_N, text_dim=100, mel=100, branches=2):
+    m = branches * (n + 1)  # + the time token
+    per_tok = depth * (2 * (4 * dim * dim + 2 * ff_mult * dim * dim) + 4 * (n + 1) * heads * 64) + (depth // 2) * 2 * 2 * dim * dim
+    return m * (per_tok + 2 * 2 * 31 * (dim // 16) * dim + 2 * (2 * mel + text_dim) * dim + 2 * dim * mel)
+
+
+def run_c4(voc, dev, stream, pk: dict, steps: int = 3, warmup: int = 2) -> dict:
+    """One 30 s utterance through the 24-layer UNetT (attention over 2801 positions is 29 % of the flops), NFE 32."""
+    import f5b200
+
+    torch.manual_seed(4)
+    un = f5b200.UNetT(dim=1024, depth=24, heads=16, ff_mult=4, text_mask_padding=False, pe_attn_head=1,
+                      text_num_embeds=59, precision="bf16")
+    cfm = f5b200.CFM(transformer=un.to(dev), mel_spec_kwargs=dict(mel_spec_type="vocos")).eval()
+    cond, text, y0 = (t.to(dev) for t in synth_inputs(4, C4_N, N_REF, C4_NTEXT))
+    kw = dict(duration=C4_N, steps=C4_NFE, cfg_strength=CFG, sway_sampling_coef=SWAY, return_trajectory=False)
+
+    def step():
+        mel, _ = cfm.sample(cond=cond, text=text, y0=y0, **kw)
+        return voc.decode(mel[:, N_REF:, :].permute(0, 2, 1).contiguous())
+
+    with torch.cuda.stream(stream):
+        for _ in range(warmup):
+            step()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            wav = step()
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        assert torch.isfinite(wav).all()
+    ms = e0.elapsed_time(e1) / steps
+    gen = C4_N - N_REF
+    fl = C4_NFE * flops_per_eval_unett()
+    del cfm, un
+    torch.cuda.empty_cache()
+    return {"workload": f"C4: E2TTS_Base UNetT (1024/24/16, ff x4) random-init, 1 utterance N={C4_N} (+1 time token, ref "
+                        f"{N_REF}), {C4_NTEXT} text tokens, NFE {C4_NFE}, CFG {CFG}, Vocos; {steps} timed after {warmup} warm-ups",
+            "ms_per_utterance": round(ms, 2), "generated_frames_per_s": round(gen / (ms / 1e3), 1),
+            "rtf": round(ms / 1e3 / (gen * HOP / SR), 6), "flops_per_utterance": fl,
+            "tflops": round(fl / (ms / 1e3) / 1e12, 1), "frac_of_sustained_peak": round(fl / (ms / 1e3) / 1e12 / pk["tf_sus"], 4)}
+
+
 # ---- our arm -------------------------------------------------------------------------------------------------------
 MEL_TOL_16BIT = 2e-2  # north star: 16-bit mode mel within 2e-2 max-abs of the fp32 reference
 
@@ -344,6 +481,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    extra_warm = 3 if world > 1 else 0
     n_in = args.warmup + args.steps
     # inputs cycle over GOLDEN_SEEDS (offset by rank): every timed utterance has a committed fp32-oracle result
     seed_of = lambda i: GOLDEN_SEEDS[(i + rank) % len(GOLDEN_SEEDS)]  # noqa: E731
@@ -370,6 +508,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         # -------- value: device-resident inputs, CUDA events on the launching stream --------
         for i in range(args.warmup):
             step_device(i)
+        for i in range(extra_warm):  # several processes start together: let clocks / allocator / page-ins settle
+            step_device(i % max(args.warmup, 1))
         barrier()
         clk = ClockSampler(local_rank)
         clk.start()
@@ -399,6 +539,17 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         d2h = w.numel() * w.element_size()
         roof = roofline_gemm(stream, pk) if rank == 0 else None
 
+    c3 = c4 = None
+    if not args.no_c3:
+        # same weights; the key mask needs attn_mask_enabled (no effect on batch 1, where the reference passes mask=None)
+        dit.attn_mask_enabled = True
+        os.environ["F5B_NO_GRAPH"] = "1"  # 18 micro-batch shapes: eager launches (measured equal to graph replay at these sizes)
+        dit.invalidate_plan()
+        c3 = run_c3(cfm, voc, dev, stream, rank, world, pk)
+        os.environ.pop("F5B_NO_GRAPH", None)
+    if rank == 0 and world == 1 and not args.no_c4:
+        dit.invalidate_plan()  # release the C2 / C3 plan's workspace first
+        c4 = run_c4(voc, dev, stream, pk)
     if rank != 0:
         return
     ms_step = ms_total / args.steps
@@ -407,7 +558,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     gen_s = GEN_FRAMES * HOP / SR
     step_tf = (NFE * flops_per_eval() + 27.0e6 * GEN_FRAMES) / (ms_step / 1e3) / 1e12
     line = {"metric": METRIC, "value": round(val, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "warmup_effective": args.warmup + extra_warm, "ms_per_step": round(ms_step, 3),
+            "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "dtype_detail": DTYPE_DETAIL, "data": "synthetic",
             "config": workload_config(world),
             "rtf": round(ms_step / 1e3 / gen_s, 5), "rtf_e2e": round(e2e_s / args.steps / gen_s, 5),
@@ -416,7 +568,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
             "step_tflops": {"achieved": round(step_tf, 1), "peak_sustained": pk["tf_sus"],
                             "frac": round(step_tf / pk["tf_sus"], 4),
                             "flops_per_step": NFE * flops_per_eval() + 27.0e6 * GEN_FRAMES},
-            "roofline": roof}
+            "roofline": roof, "c3": c3, "c4": c4}
     if world == 1 and not args.no_cpu:
         state = {k: v.detach().float().cpu() for k, v in dit.state_dict().items()}
         vstate = {k: v.detach().float().cpu() for k, v in voc.state_dict().items()}
@@ -432,6 +584,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-c1", action="store_true", help="reference arm: skip the C1 (F5TTS_Small) CPU run")
+    ap.add_argument("--no-c3", action="store_true", help="skip the C3 record (256 utterances, sharded over the ranks)")
+    ap.add_argument("--no-c4", action="store_true", help="skip the C4 record (E2TTS_Base 30 s, N=1 only)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -88,6 +88,11 @@ int f5b_forward(f5b_plan* plan, const float* x, const float* cond, const int64_t
                 const int32_t* durations, int32_t B, int32_t N, int32_t nt, int32_t drop_audio_cond, int32_t drop_text,
                 int32_t cfg_infer, int32_t cache, float* out, int32_t mem, void* stream);
 int f5b_clear_cache(f5b_plan* plan);
+/* Calls whose buffers are on the device (mem = F5B_MEM_DEVICE) return once their work is enqueued on `stream`, like
+ * any PyTorch CUDA operator; with host buffers they are synchronous.  f5b_plan_sync waits for the plan's last call and
+ * returns its deferred status: F5B_ERR_INDEX when an asynchronous call met a text id outside the embedding table
+ * (otherwise that error is returned by the next call on the plan, once the offending one has completed). */
+int f5b_plan_sync(f5b_plan* plan);
 
 /* Replaces the forward half of CFM.forward (model/cfm.py:231-302), i.e. the flow-matching loss of one training batch
  * after the random draws (which stay host-side Python like the reference's): phi = (1 - t) x0 + t x1, cond = x1 outside
@@ -115,12 +120,22 @@ int f5b_ref_audio(const float* wav, int32_t channels, int64_t nw, const float* t
 int f5b_vocos_create(const f5b_tensor* weights, int32_t n_weights, int32_t mode, int32_t device, f5b_vocos** out);
 void f5b_vocos_destroy(f5b_vocos* v);
 int f5b_vocos_decode(f5b_vocos* v, const float* mel, int32_t B, int32_t T, float* wav, int32_t mem, void* stream);
+/* The same over a batch of utterances of different length (the request level decodes a whole micro-batch in one call):
+ * lens [B] int32 (same memory space as mel; NULL = all T): row b holds lens[b] frames, the convolutions' zero padding
+ * applies at ITS end; wav [B, (T-1)*256], row b valid up to (lens[b]-1)*256 samples, zeros after. */
+int f5b_vocos_decode_varlen(f5b_vocos* v, const float* mel, const int32_t* lens, int32_t B, int32_t T, float* wav,
+                            int32_t mem, void* stream);
 
 /* Kernel-level entry points used by the parity tests and the roofline benchmark (device pointers only).
  *   gemm:      out[M,N] = act(A[M,K] W[N,K]^T + bias); mode selects fp32 SIMT or bf16 tcgen05 (inputs fp32, converted)
  *   attention: qkv [batches*rows, 3*heads*64] fp32 -> out [batches*rows, heads*64] fp32 */
 int f5b_op_gemm(int32_t mode, const float* A, const float* W, const float* bias, int32_t M, int32_t N, int32_t K,
                 int32_t act, float* out, int32_t force_bn, int32_t device, void* stream);
+/* istft: the Vocos ISTFTHead after its linear layer (exp, clip 1e2, cos / sin, irFFT 1024, Hann, overlap-add, envelope,
+ *            trim): z [B*T, ldz] (cols [0,513) log-magnitude, [513,1026) phase), lens [B] or NULL -> wav [B, (T-1)*256].
+ *            Witnesses in the reference: runtime/triton_trtllm/scripts/export_vocoder_to_onnx.py:51-59, conv_stft.py:193-234. */
+int f5b_op_istft(const float* z, int64_t ldz, const int32_t* lens, int32_t B, int32_t T, float* wav, int32_t device,
+                 void* stream);
 int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int32_t batches, int32_t rows,
                      int32_t heads, float* out, int32_t device, void* stream);
 /* Times `iters` back-to-back launches of one kernel with CUDA events on `stream`; returns average ms in *ms.

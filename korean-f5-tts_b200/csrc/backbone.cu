@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "plan.h"
 
@@ -108,7 +109,13 @@ struct f5b_plan {
   int ada_W = 0;
   float *inv_freq_text, *inv_freq_rope, *time_freq;
   int* bad_id_dev = nullptr;   // set by text_lookup on a token id outside the embedding table
-  int* bad_id_host = nullptr;  // pinned mirror, read after the call's synchronisation
+  int* bad_id_host = nullptr;  // pinned mirror, read once the call that wrote it has completed
+  // Calls with device-resident buffers return as soon as their work is enqueued (like every PyTorch CUDA op): `done`
+  // marks the end of the last call (the next call on ANY stream orders itself after it: the workspace is shared), a
+  // bad token id of an asynchronous call is reported by the next call / f5b_plan_sync once `done` has completed.
+  cudaEvent_t done = nullptr, fork = nullptr;
+  bool pending = false;
+  std::mutex mu;               // one call at a time per plan (the reference calls sample() from a thread pool)
   // forward-API text cache
   bool cache_valid = false;
   int cache_key[6] = {0, 0, 0, 0, 0, 0};
@@ -142,6 +149,8 @@ struct f5b_plan {
 f5b_plan::~f5b_plan() {
   drop_graph();
   if (bad_id_host) cudaFreeHost(bad_id_host);
+  if (done) cudaEventDestroy(done);
+  if (fork) cudaEventDestroy(fork);
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 
@@ -273,6 +282,8 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
   F5B_CHECK_CUDA(cudaMemset(bad_id_dev, 0, sizeof(int)));
   F5B_CHECK_CUDA(cudaHostAlloc(&bad_id_host, sizeof(int), cudaHostAllocDefault));
   *bad_id_host = 0;
+  F5B_CHECK_CUDA(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+  F5B_CHECK_CUDA(cudaEventCreateWithFlags(&fork, cudaEventDisableTiming));
   if (!ft.empty()) F5B_CHECK_CUDA(cudaMemcpy(inv_freq_text, ft.data(), ft.size() * 4, cudaMemcpyHostToDevice));
   F5B_CHECK_CUDA(cudaMemcpy(inv_freq_rope, fr.data(), 32 * 4, cudaMemcpyHostToDevice));
   F5B_CHECK_CUDA(cudaMemcpy(time_freq, tf.data(), 128 * 4, cudaMemcpyHostToDevice));

@@ -564,7 +564,9 @@ void tc_gemm_init_kernels() {
 static void pick_tiling(long long tiles_m_per_batch, int batches, int N, int K, int sms, bool can_split, bool can_pair,
                         int force_bn, int force_pair, int force_splits, int* bn_out, int* pair_out, int* splits_out) {
   const int cand[4] = {64, 128, 192, 256};
-  const double kb_us[2][4] = {{0.26, 0.28, 0.35, 0.43}, {9.9, 0.20, 0.23, 0.27}};
+  // pair row: ratios to the single-CTA row measured on B200 after the elect.sync issue fix (profiles/r2_gemm_sweep.log,
+  // M = 32768: 0.99 / 0.92 / 0.88 per k-block round at 128 / 192 / 256 columns, each round covering 256 rows)
+  const double kb_us[2][4] = {{0.26, 0.28, 0.35, 0.43}, {9.9, 0.277, 0.322, 0.378}};
   const double epi_us[4] = {0.8, 1.4, 2.4, 2.5};
   const int num_kb = (K + BK - 1) / BK;
   double best_cost = 1e30;
@@ -583,7 +585,7 @@ static void pick_tiling(long long tiles_m_per_batch, int batches, int N, int K, 
         const long long units = mrows * batches * ((N + cand[i] - 1) / cand[i]) * sp;
         const long long workers = pair ? sms / 2 : sms;
         const long long rounds = (units + workers - 1) / workers;
-        const double cost = rounds * (kb_us[pair][i] * ((num_kb + sp - 1) / sp) + 0.15) + epi_us[i] + (pair ? 0.1 : 0.0);
+        const double cost = rounds * (kb_us[pair][i] * ((num_kb + sp - 1) / sp) + 0.15) + epi_us[i] + (pair ? 0.6 : 0.0);
         if (cost < best_cost) {
           best_cost = cost;
           *bn_out = cand[i];
@@ -623,8 +625,10 @@ void tc_gemm(cudaStream_t st, int sm_count, const bf16* A, long long lda, int ro
     static const bool allow_split = std::getenv("F5B_SPLIT_K") != nullptr;
     const bool can_split = ep.kind == EPI_RESID && ep.act == ACT_NONE && (allow_split || force_splits > 1);
     // force_bn: 0 = model's choice, 64..256 = that width on single CTAs, 1000 + width = that width on CTA pairs
-    static const bool no_pair = std::getenv("F5B_PAIR") == nullptr;  // measured slower than single CTAs so far: opt-in
+    // CTA pairs win from M ~ 5 k rows on (qkv at M = 32768: 1365 vs 1200 TFLOP/s) since the single-lane roles issue
+    // through elect.sync; F5B_NO_PAIR=1 switches them off
     const int fpair = force_bn >= 1000 ? 1 : force_bn > 0 ? 0 : -1;
+    static const bool no_pair = std::getenv("F5B_NO_PAIR") != nullptr;
     pick_tiling(s.tiles_m_per_batch, batches, N, K, sm_count, can_split, !no_pair || fpair == 1, force_bn % 1000, fpair, force_splits,
                 &bn, &pair, &s.splits);
     a_cols = K;

@@ -47,6 +47,7 @@ _SIGNATURES = {
                               C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32,
                               C.c_void_p]),
     "f5b_clear_cache": (C.c_int, [C.c_void_p]),
+    "f5b_plan_sync": (C.c_int, [C.c_void_p]),
     "f5b_mel": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "f5b_ref_audio": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                 C.c_float, C.c_void_p, C.c_int64, C.POINTER(C.c_float), C.c_int32, C.c_int32,
@@ -54,6 +55,9 @@ _SIGNATURES = {
     "f5b_vocos_create": (C.c_int, [C.POINTER(Tensor), C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     "f5b_vocos_destroy": (None, [C.c_void_p]),
     "f5b_vocos_decode": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
+    "f5b_vocos_decode_varlen": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32,
+                                          C.c_void_p]),
+    "f5b_op_istft": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p]),
     "f5b_op_gemm": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                               C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "f5b_op_attention": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,

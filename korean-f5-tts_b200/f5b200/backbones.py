@@ -180,6 +180,13 @@ class _PlanBackbone(nn.Module):
         self._plan_sig = sig
         return handle
 
+    def synchronize(self):
+        """Wait for the plan's last call and raise its deferred error.  Calls on CUDA tensors return once their work is
+        enqueued (like any PyTorch CUDA operator); a token id outside the embedding table -- `nn.Embedding` would raise
+        IndexError (dit.py:42,94) -- then surfaces here, or in the next call on this module."""
+        if self._plan is not None:
+            _lib.check(_lib.lib().f5b_plan_sync(self._plan))
+
     def clear_cache(self):
         if self._plan is not None:
             _lib.lib().f5b_clear_cache(self._plan)

@@ -178,13 +178,18 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
                                       duration=dur if b > 1 else int(dur[0]), steps=nfe_step,
                                       cfg_strength=cfg_strength, sway_sampling_coef=sway_sampling_coef, y0=y0,
                                       return_trajectory=False)
+            # the whole micro-batch through Vocos in ONE call (per-row lengths: each row is decoded as if alone), one
+            # device -> host copy per micro-batch instead of a decode + .cpu() per chunk
+            gen = out[:, ref_audio_len:, :].to(torch.float32).permute(0, 2, 1).contiguous()  # [b, 100, n - ref]
+            glen = torch.tensor([eff[i] - ref_audio_len for i in g], dtype=torch.int32)
+            wav = vocoder.decode(gen, glen.to(device)) if b > 1 else vocoder.decode(gen)
+            if rms < target_rms:
+                wav = wav * rms / target_rms
+            wav_h, gen_h = wav.cpu().numpy(), gen.cpu().numpy()
             for r, i in enumerate(g):
-                gen = out[r:r + 1, ref_audio_len:eff[i], :].to(torch.float32).permute(0, 2, 1).contiguous()
-                wav = vocoder.decode(gen)
-                if rms < target_rms:
-                    wav = wav * rms / target_rms
-                waves[i] = wav.squeeze().cpu().numpy()
-                mels[i] = gen[0].cpu().numpy()
+                t_i = int(glen[r])
+                waves[i] = wav_h[r, : (t_i - 1) * hop_length]
+                mels[i] = gen_h[r, :, :t_i]
 
     if streaming:
         for w in waves:

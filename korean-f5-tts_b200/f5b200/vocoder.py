@@ -85,15 +85,18 @@ class Vocos(nn.Module):
         return h
 
     @torch.no_grad()
-    def decode(self, mel: torch.Tensor) -> torch.Tensor:
-        """mel [b, 100, T] -> waveform [b, (T - 1) * 256]."""
+    def decode(self, mel: torch.Tensor, lens: torch.Tensor | None = None) -> torch.Tensor:
+        """mel [b, 100, T] -> waveform [b, (T - 1) * 256].  `lens` [b] (extra): row i holds lens[i] <= T frames -- it is
+        decoded exactly as if it were alone (the convolutions' zero padding sits at ITS end); row i of the result is
+        valid up to (lens[i] - 1) * 256 samples and zero after.  On CUDA tensors the call returns once enqueued."""
         h = self.handle()
         m = mel.to(torch.float32).contiguous()
         b, c, t = m.shape
         assert c == VOCOS_CFG["n_mels"]
         wav = torch.empty((b, (t - 1) * VOCOS_CFG["hop"]), device=m.device, dtype=torch.float32)
-        _lib.check(_lib.lib().f5b_vocos_decode(h, m.data_ptr(), b, t, wav.data_ptr(), _lib.mem_kind(m),
-                                               _lib.current_stream_ptr(m.device)))
+        ln = None if lens is None else lens.to(device=m.device, dtype=torch.int32).contiguous()
+        _lib.check(_lib.lib().f5b_vocos_decode_varlen(h, m.data_ptr(), _lib.ptr(ln), b, t, wav.data_ptr(),
+                                                      _lib.mem_kind(m), _lib.current_stream_ptr(m.device)))
         return wav
 
     forward = decode

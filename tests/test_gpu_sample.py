@@ -164,12 +164,64 @@ def test_vocos_decode(T, B):
     assert s >= 40.0  # bf16 mode: waveform SNR >= 40 dB versus the fp32 reference
 
 
+def test_vocos_varlen_batch_equals_each_row_alone():
+    """One decode call over rows of different length (`lens`) = every row decoded by itself (oracle), zeros after."""
+    import f5b200
+
+    sd = O.synth_vocos_weights(2)
+    lens = [57, 120, 9, 2, 77]
+    T = max(lens)
+    g = torch.Generator().manual_seed(5)
+    mel = (torch.randn(len(lens), 100, T, generator=g) * 2.0 - 3.0).clamp(min=-11.5)  # garbage beyond each row's length
+    for precision, tol in (("fp32", 1e-3), ("bf16", None)):
+        voc = f5b200.Vocos(precision=precision)
+        voc.load_state_dict(sd)
+        wav = voc.cuda().decode(mel.cuda(), torch.tensor(lens)).cpu()
+        assert tuple(wav.shape) == (len(lens), (T - 1) * 256)
+        for r, n in enumerate(lens):
+            ref = O.vocos_decode(sd, mel[r:r + 1, :, :n])[0]
+            got = wav[r, : (n - 1) * 256]
+            if tol is not None:
+                assert max_abs(got, ref) <= tol * max(1.0, float(ref.abs().max())), (precision, r)
+            else:
+                from helpers import snr_db
+                assert snr_db(ref, got) >= 40.0, (precision, r)
+            assert float(wav[r, (n - 1) * 256:].abs().max() if n < T else 0.0) == 0.0
+
+
+def test_istft_head_matches_reference_witness(golden_dir):
+    """The fused ISTFTHead kernel against the reference's own implementation of that arithmetic (ISTFTHead over
+    conv_stft.STFT.inverse, run unmodified by oracle/make_golden_vocos.py): first (T - 1) * 256 samples, 1e-3 bound."""
+    import ctypes as C
+    import os
+
+    import numpy as np
+    from f5b200 import _lib as L
+
+    g = np.load(os.path.join(golden_dir, "vocos_head_istft.npz"))
+    w, b = torch.from_numpy(g["head.out.weight"]), torch.from_numpy(g["head.out.bias"])
+    for tag in "abcd":
+        h, want = torch.from_numpy(g["h_" + tag]), torch.from_numpy(g["audio_" + tag])
+        z = torch.nn.functional.pad(h[0] @ w.T + b, (0, 2)).cuda().contiguous()  # [T, 1028]: the head's linear layer
+        T = z.shape[0]
+        wav = torch.empty((1, (T - 1) * 256), device="cuda")
+        L.check(L.lib().f5b_op_istft(z.data_ptr(), z.shape[1], None, 1, T, wav.data_ptr(), 0, 0))
+        err = max_abs(wav, want[:, : (T - 1) * 256])
+        assert err <= 1e-3 * max(1.0, float(want.abs().max())), (tag, err)
+
+
 def test_missing_weight_is_loud():
     import f5b200
 
     m = f5b200.DiT(dim=128, depth=1, heads=2, ff_mult=2, text_dim=64, conv_layers=1, text_num_embeds=10, precision="fp32")
     with pytest.raises(f5b200.F5BError):
         m(torch.zeros(1, 8, 100), torch.zeros(1, 8, 100), torch.zeros(1, 3, dtype=torch.long), torch.tensor(0.5))
+
+
+def f5b200_cpu_inputs(cfm, cond, text):
+    """(y0, step_cond, text, durations, t, steps, cfg, want_traj) with HOST tensors: the C ABI stages them itself."""
+    p = cfm.prepare_inputs(cond, text, 40, steps=2, sway_sampling_coef=None, seed=1, y0=torch.zeros(1, 40, 100))
+    return p["y0"], p["step_cond"], p["text"], None, p["t"], p["steps"], 2.0, False
 
 
 def test_text_id_out_of_range_raises_index_error():
@@ -183,7 +235,14 @@ def test_text_id_out_of_range_raises_index_error():
     for bad_id in (10, 4000, -2):  # valid ids are -1 (padding) .. text_num_embeds - 1
         bad = text.clone()
         bad[0, 2] = bad_id
+        # CUDA tensors: the call is asynchronous (like nn.Embedding's device-side assert, the error surfaces at the next
+        # synchronisation point of the module -- or in its next call)
+        cfm.sample(cond=cond.cuda(), text=bad.cuda(), duration=40, steps=2, cfg_strength=2.0, seed=1)
         with pytest.raises(IndexError):
-            cfm.sample(cond=cond.cuda(), text=bad.cuda(), duration=40, steps=2, cfg_strength=2.0, seed=1)
+            cfm.transformer.synchronize()
+        # host tensors: synchronous, raised by the call itself
+        host = f5b200_cpu_inputs(cfm, cond, bad)
+        with pytest.raises(IndexError):
+            cfm._ode(*host)
     again, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), duration=40, steps=2, cfg_strength=2.0, seed=1)
     assert torch.equal(good, again)

@@ -154,7 +154,20 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
 
     ragged_ok = bool(getattr(model_obj.transformer, "attn_mask_enabled", False))
     order = list(range(len(eff)))
-    if ragged_ok:
+    if streaming:
+        # audio must leave in text order and the FIRST piece as early as possible (socket_server.py:138-177): the first
+        # chunk runs alone, the rest in consecutive (unsorted) runs, each run one sample() + one Vocos call
+        groups, cur = [[0]], []
+        for i in order[1:]:
+            can_join = cur and (ragged_ok or eff[i] == eff[cur[0]]) and len(cur) < max_batch and \
+                (len(cur) + 1) * max(eff[i], max(eff[k] for k in cur)) <= max_rows
+            if cur and not can_join:
+                groups.append(cur)
+                cur = []
+            cur.append(i)
+        if cur:
+            groups.append(cur)
+    elif ragged_ok:
         groups = micro_batches(order, eff, max_rows=max_rows, max_batch=max_batch)
     else:  # equal-length rows may still share a batch
         by_len: dict = {}
@@ -162,9 +175,10 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
             by_len.setdefault(eff[i], []).append(i)
         groups = [g[k:k + max_batch] for g in by_len.values() for k in range(0, len(g), max_batch)]
 
-    mels: List[torch.Tensor | None] = [None] * len(eff)
-    waves: List[np.ndarray | None] = [None] * len(eff)
-    for g in (progress.tqdm(groups) if progress is not None else groups):
+    def launch(g):
+        """Enqueue one micro-batch: sample() + ONE Vocos call over its rows (per-row lengths: each row is decoded as if
+        alone) + device -> pinned-host copies.  Nothing here waits for the GPU (the C ABI is asynchronous for device
+        buffers); the returned event marks the copies' end."""
         b, n = len(g), max(eff[i] for i in g)
         nt = max(len(ids[i]) for i in g)
         text = torch.full((b, nt), -1, dtype=torch.long)
@@ -173,27 +187,44 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
             text[r, :len(ids[i])] = ids[i]
             y0[r, :eff[i]] = noise[i]
         dur = torch.tensor([durations[i] for i in g], device=device, dtype=torch.long)
+        glen = torch.tensor([eff[i] - ref_audio_len for i in g], dtype=torch.int32)
         with torch.inference_mode():
             out, _ = model_obj.sample(cond=ref_mel.expand(b, -1, -1).contiguous(), text=text.to(device),
                                       duration=dur if b > 1 else int(dur[0]), steps=nfe_step,
                                       cfg_strength=cfg_strength, sway_sampling_coef=sway_sampling_coef, y0=y0,
                                       return_trajectory=False)
-            # the whole micro-batch through Vocos in ONE call (per-row lengths: each row is decoded as if alone), one
-            # device -> host copy per micro-batch instead of a decode + .cpu() per chunk
             gen = out[:, ref_audio_len:, :].to(torch.float32).permute(0, 2, 1).contiguous()  # [b, 100, n - ref]
-            glen = torch.tensor([eff[i] - ref_audio_len for i in g], dtype=torch.int32)
             wav = vocoder.decode(gen, glen.to(device)) if b > 1 else vocoder.decode(gen)
             if rms < target_rms:
                 wav = wav * rms / target_rms
-            wav_h, gen_h = wav.cpu().numpy(), gen.cpu().numpy()
-            for r, i in enumerate(g):
-                t_i = int(glen[r])
-                waves[i] = wav_h[r, : (t_i - 1) * hop_length]
-                mels[i] = gen_h[r, :, :t_i]
+            wav_h = torch.empty(wav.shape, dtype=wav.dtype, pin_memory=True)
+            gen_h = torch.empty(gen.shape, dtype=gen.dtype, pin_memory=True)
+            wav_h.copy_(wav, non_blocking=True)
+            gen_h.copy_(gen, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+        return g, glen, wav_h, gen_h, ev
 
+    def collect(handle):
+        g, glen, wav_h, gen_h, ev = handle
+        ev.synchronize()
+        wav_n, gen_n = wav_h.numpy(), gen_h.numpy()
+        return [(i, wav_n[r, : (int(glen[r]) - 1) * hop_length], gen_n[r, :, : int(glen[r])]) for r, i in enumerate(g)]
+
+    # two micro-batches in flight: while the host hands out (or cross-fades) batch k, the GPU already works on k + 1
+    mels: List[np.ndarray | None] = [None] * len(eff)
+    waves: List[np.ndarray | None] = [None] * len(eff)
+    it = iter(progress.tqdm(groups) if progress is not None else groups)
+    pending = launch(next(it))
+    while pending is not None:
+        g_next = next(it, None)
+        nxt = launch(g_next) if g_next is not None else None
+        for i, w, m in collect(pending):
+            waves[i], mels[i] = w, m
+            if streaming:  # (groups are consecutive and in order)
+                for j in range(0, len(w), chunk_size):
+                    yield w[j:j + chunk_size], target_sample_rate
+        pending = nxt
     if streaming:
-        for w in waves:
-            for j in range(0, len(w), chunk_size):
-                yield w[j:j + chunk_size], target_sample_rate
         return
     yield cross_fade(waves, cross_fade_duration), target_sample_rate, np.concatenate(mels, axis=1)

@@ -387,6 +387,50 @@ def run_c3(cfm, voc, dev, stream, rank: int, world: int, pk: dict) -> dict:
             "frac_of_sustained_peak": round(flops / t_job / world / 1e12 / pk["tf_sus"], 4)}
 
 
+# ---- f4: streaming request through the serving surface (first-chunk latency) ------------------------------------------
+def run_f4(cfm, voc, dev) -> dict:
+    """One streaming request through f5b200.serving.TTSStreamingProcessor (the reference's socket_server protocol, NFE 32
+    like its defaults): 3 s prompt, a paragraph that the first-package rule cuts into several chunks; the sink records
+    when the first float32 PCM bytes leave and when b"END" does.  The reference's only published serving number is the
+    Triton client-server latency (253 ms average on an L20, README.md:122-129)."""
+    from f5b200 import serving, tokenizers
+
+    vocab = {c: i for i, c in enumerate(" abcdefghijklmnopqrstuvwxyz,.?!;:'-ABCDEFGHIJKLMNOPQRSTU")}
+    assert len(vocab) == 58
+    cfm.vocab_char_map = vocab
+    g = torch.Generator().manual_seed(7)
+    audio = torch.randn(1, 3 * SR, generator=g) * 0.05
+
+    class Sink:
+        def __init__(self):
+            self.t, self.n = [], 0
+
+        def sendall(self, b):
+            self.t.append(time.perf_counter())
+            self.n += len(b)
+
+    proc = serving.TTSStreamingProcessor(cfm, voc, (audio, SR), "this is the reference prompt, three seconds long.",
+                                         device=dev, tokenize=tokenizers.char_tokens, nfe_step=32, warm_up=True)
+    text = ("The first sentence is short. Then the speaker goes on for a while, describing the weather and the road. "
+            "After that, a question follows: is anybody listening? Finally, the paragraph ends with a longer remark "
+            "about nothing in particular, just to fill the second batch.")
+    res = []
+    for _ in range(3):  # first request of a session (short first package), repeated on fresh sessions
+        proc.first_package = True
+        sink = Sink()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        proc.generate_stream(text, sink)
+        res.append((sink.t[0] - t0, sink.t[-1] - t0, (sink.n - 3) // 4))
+    first, total, samples = min(res)
+    cfm.vocab_char_map = None
+    return {"workload": "streaming request (socket_server protocol: float32 PCM pieces of 2048 samples, END), C2 model, "
+                        "3 s prompt, 4-sentence paragraph, NFE 32, CFG 2.0, first chunk alone + later chunks batched",
+            "text_chunks": len(serving.TTSStreamingProcessor.text_batches(proc, text)) if setattr(proc, "first_package", True) is None else None,
+            "first_chunk_ms": round(first * 1e3, 2), "total_ms": round(total * 1e3, 2),
+            "audio_s": round(samples / SR, 2), "rtf": round(total / (samples / SR), 5)}
+
+
 # ---- C4: E2TTS_Base flat-UNet transformer, ~30 s (BASELINE.json configs[3]) ------------------------------------------
 C4_N, C4_NTEXT, C4_NFE = 2800, 500, 32
 
@@ -539,13 +583,15 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         d2h = w.numel() * w.element_size()
         roof = roofline_gemm(stream, pk) if rank == 0 else None
 
-    c3 = c4 = None
+    c3 = c4 = f4 = None
     if not args.no_c3:
         # same weights; the key mask needs attn_mask_enabled (no effect on batch 1, where the reference passes mask=None)
         dit.attn_mask_enabled = True
         os.environ["F5B_NO_GRAPH"] = "1"  # 18 micro-batch shapes: eager launches (measured equal to graph replay at these sizes)
         dit.invalidate_plan()
         c3 = run_c3(cfm, voc, dev, stream, rank, world, pk)
+        if rank == 0 and world == 1:
+            f4 = run_f4(cfm, voc, dev)
         os.environ.pop("F5B_NO_GRAPH", None)
     if rank == 0 and world == 1 and not args.no_c4:
         dit.invalidate_plan()  # release the C2 / C3 plan's workspace first
@@ -568,7 +614,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
             "step_tflops": {"achieved": round(step_tf, 1), "peak_sustained": pk["tf_sus"],
                             "frac": round(step_tf / pk["tf_sus"], 4),
                             "flops_per_step": NFE * flops_per_eval() + 27.0e6 * GEN_FRAMES},
-            "roofline": roof, "c3": c3, "c4": c4}
+            "roofline": roof, "c3": c3, "c4": c4, "f4_streaming": f4}
     if world == 1 and not args.no_cpu:
         state = {k: v.detach().float().cpu() for k, v in dit.state_dict().items()}
         vstate = {k: v.detach().float().cpu() for k, v in voc.state_dict().items()}

@@ -64,8 +64,9 @@ struct Layer {
 };
 
 struct Bufs {
-  long long cap_rows = 0;  // batches * R
-  int capB = 0, cap_nt = 0, cap_steps = 0, capN = 0;
+  long long cap_rows = 0;  // capacities, each for one quantity (see ensure_ws): 2 B R, B N, B nt, table rows
+  long long cap_bn = 0, cap_bnt = 0, cap_nT = 0;
+  int capB = 0, capR = 0;
   float *y, *y2, *cond, *v_out, *x, *hproj, *hconst, *a_in, *te, *sin_emb, *h1, *st_emb, *ada, *rope_cs, *t_dev, *grn_scratch, *traj;
   long long traj_cap = 0;
   long long* text;
@@ -294,65 +295,79 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
 // workspace
 // ---------------------------------------------------------------------------------------------
 void f5b_plan::ensure_ws(int B, int N, int nt, int steps, bool want_traj) {
+  // Capacities are tracked per QUANTITY (rows, B * N, B * nt, table rows, ...) and only ever grow: a job whose
+  // micro-batches trade batch size against length (C3: B = 8 x N = 1874 ... B = 57 x N = 285, always ~16 k rows) used
+  // to re-allocate the whole workspace -- device-wide synchronisation, ~45 cudaMalloc / cudaFree of up to hundreds of MB
+  // -- at EVERY call, because one request-shaped key (B, N, ...) never covered the next one.
   const int R = N + R_extra;
-  const long long rows = 2LL * B * R;
+  const long long rows = 2LL * B * R, bn = (long long)B * N, bnt = (long long)B * (nt > 0 ? nt : 1);
+  const long long nT = steps > 2 * B ? steps : 2 * B;  // table rows: steps (sample) or B (forward)
   const long long traj_need = want_traj ? (long long)(steps + 1) * B * N * a.mel_dim : 0;
-  if (wk && rows <= bf.cap_rows && B <= bf.capB && nt <= bf.cap_nt && steps <= bf.cap_steps && N <= bf.capN &&
-      traj_need <= bf.traj_cap)
+  if (wk && rows <= bf.cap_rows && bn <= bf.cap_bn && bnt <= bf.cap_bnt && B <= bf.capB && nT <= bf.cap_nT &&
+      R <= bf.capR && traj_need <= bf.traj_cap)
     return;
   drop_graph();
   cache_valid = false;
   F5B_CHECK_CUDA(cudaDeviceSynchronize());
+  Bufs nb;
+  auto grow = [](long long need, long long have) {  // 1/8 headroom when growing: slightly longer requests fit
+    return need <= have ? have : need + need / 8;
+  };
+  nb.cap_rows = grow(rows, wk ? bf.cap_rows : 0);
+  nb.cap_bn = grow(bn, wk ? bf.cap_bn : 0);
+  nb.cap_bnt = grow(bnt, wk ? bf.cap_bnt : 0);
+  nb.capB = (int)grow(B, wk ? bf.capB : 0);
+  nb.cap_nT = grow(nT, wk ? bf.cap_nT : 0);
+  nb.capR = (int)grow(R, wk ? bf.capR : 0);
+  nb.traj_cap = traj_need <= (wk ? bf.traj_cap : 0) ? bf.traj_cap : traj_need;
   // The old arena goes first (peak memory stays at one workspace); until every allocation below has succeeded the
   // plan holds NO workspace and zero capacities, so a failed growth (OOM on a large request) cannot leave stale
   // pointers behind a passing capacity check: the next call simply allocates again.
   wk.reset();
-  bf = Bufs();
+  this->bf = Bufs();
   std::unique_ptr<Arena> fresh(new Arena());
   Arena& A = *fresh;
-  Bufs nb;
   Bufs& bf = nb;  // (shadows the member on purpose: everything below fills the local copy)
   const int d = a.dim, mel = a.mel_dim, ffd = a.dim * a.ff_mult;
   const size_t es = ctx.mode == F5B_MODE_BF16 ? 2 : 4;
-  const int nT = steps > 2 * B ? steps : 2 * B;  // table rows: steps (sample) or B (forward)
-  bf.cap_rows = rows; bf.capB = B; bf.cap_nt = nt; bf.cap_steps = steps; bf.capN = N; bf.traj_cap = traj_need;
-  bf.y = A.alloc_n<float>((size_t)B * N * mel);
-  bf.y2 = A.alloc_n<float>((size_t)B * N * mel);
-  bf.cond = A.alloc_n<float>((size_t)B * N * mel);
-  bf.v_out = A.alloc_n<float>((size_t)2 * B * R * mel);  // UNetT keeps the time-token row; consumers skip it
-  bf.x = A.alloc_n<float>((size_t)rows * d);
-  bf.hproj = A.alloc_n<float>((size_t)rows * d);
-  bf.te = A.alloc_n<float>((size_t)2 * B * N * td);
-  bf.sin_emb = A.alloc_n<float>((size_t)nT * 256);
-  bf.h1 = A.alloc_n<float>((size_t)nT * d);
-  bf.st_emb = A.alloc_n<float>((size_t)nT * d);
-  bf.ada = A.alloc_n<float>((size_t)nT * (ada_W > 0 ? ada_W : 1));
-  bf.rope_cs = A.alloc_n<float>((size_t)R * 64);
-  bf.t_dev = A.alloc_n<float>((size_t)nT + 1);
-  bf.grn_scratch = A.alloc_n<float>((size_t)2 * B * 2 * 2 * td);
-  bf.traj = traj_need ? A.alloc_n<float>((size_t)traj_need) : nullptr;
-  bf.text = A.alloc_n<long long>((size_t)B * (nt > 0 ? nt : 1));
-  bf.lens_in = A.alloc_n<int>((size_t)B);
-  bf.lens2 = A.alloc_n<int>((size_t)2 * B);
-  bf.lens2p1 = A.alloc_n<int>((size_t)2 * B);
-  bf.keep = A.alloc_n<unsigned char>((size_t)2 * B * N);
-  bf.hconst = A.alloc_n<float>((size_t)2 * B * N * d);
-  bf.a_in = A.alloc_n<float>((size_t)2 * B * N * kin_ld);
-  F5B_CHECK_CUDA(cudaMemset(bf.a_in, 0, (size_t)2 * B * N * kin_ld * 4));
-  bf.c_in = A.alloc((size_t)rows * d * es);
-  bf.c_mid = A.alloc((size_t)rows * d * es);
-  bf.norm = A.alloc((size_t)rows * d * es);
-  bf.norm3 = ctx.mode == F5B_MODE_BF16 ? A.alloc((size_t)rows * 3 * d * 2) : nullptr;
-  bf.qkv = A.alloc((size_t)rows * 3 * inner * es);
-  bf.attn_o = A.alloc((size_t)rows * inner * es);
-  bf.ffh = A.alloc((size_t)rows * ffd * es);
-  bf.tnorm = A.alloc((size_t)2 * B * N * td * es);
-  bf.th = A.alloc((size_t)2 * B * N * 2 * td * es);
+  const size_t crows = (size_t)bf.cap_rows, cbn = (size_t)bf.cap_bn, cT = (size_t)bf.cap_nT, cB = (size_t)bf.capB;
+  bf.y = A.alloc_n<float>(cbn * mel);
+  bf.y2 = A.alloc_n<float>(cbn * mel);
+  bf.cond = A.alloc_n<float>(cbn * mel);
+  bf.v_out = A.alloc_n<float>(crows * mel);  // UNetT keeps the time-token row; consumers skip it
+  bf.x = A.alloc_n<float>(crows * d);
+  bf.hproj = A.alloc_n<float>(crows * d);
+  bf.te = A.alloc_n<float>(2 * cbn * td);
+  bf.sin_emb = A.alloc_n<float>(cT * 256);
+  bf.h1 = A.alloc_n<float>(cT * d);
+  bf.st_emb = A.alloc_n<float>(cT * d);
+  bf.ada = A.alloc_n<float>(cT * (ada_W > 0 ? ada_W : 1));
+  bf.rope_cs = A.alloc_n<float>((size_t)bf.capR * 64);
+  bf.t_dev = A.alloc_n<float>(cT + 1);
+  bf.grn_scratch = A.alloc_n<float>(2 * cB * 2 * 2 * td);
+  bf.traj = bf.traj_cap ? A.alloc_n<float>((size_t)bf.traj_cap) : nullptr;
+  bf.text = A.alloc_n<long long>((size_t)bf.cap_bnt);
+  bf.lens_in = A.alloc_n<int>(cB);
+  bf.lens2 = A.alloc_n<int>(2 * cB);
+  bf.lens2p1 = A.alloc_n<int>(2 * cB);
+  bf.keep = A.alloc_n<unsigned char>(2 * cbn);
+  bf.hconst = A.alloc_n<float>(2 * cbn * d);
+  bf.a_in = A.alloc_n<float>(2 * cbn * kin_ld);
+  F5B_CHECK_CUDA(cudaMemset(bf.a_in, 0, 2 * cbn * kin_ld * 4));
+  bf.c_in = A.alloc(crows * d * es);
+  bf.c_mid = A.alloc(crows * d * es);
+  bf.norm = A.alloc(crows * d * es);
+  bf.norm3 = ctx.mode == F5B_MODE_BF16 ? A.alloc(crows * 3 * d * 2) : nullptr;
+  bf.qkv = A.alloc(crows * 3 * inner * es);
+  bf.attn_o = A.alloc(crows * inner * es);
+  bf.ffh = A.alloc(crows * ffd * es);
+  bf.tnorm = A.alloc(2 * cbn * td * es);
+  bf.th = A.alloc(2 * cbn * 2 * td * es);
   bf.skips.clear();
   bf.cat = nullptr;
   if (!is_dit) {
-    bf.cat = A.alloc((size_t)rows * 2 * d * es);
-    for (int i = 0; i < a.depth / 2; ++i) bf.skips.push_back(A.alloc_n<float>((size_t)rows * d));
+    bf.cat = A.alloc(crows * 2 * d * es);
+    for (int i = 0; i < a.depth / 2; ++i) bf.skips.push_back(A.alloc_n<float>(crows * d));
   }
   this->bf = nb;  // commit: every allocation succeeded
   wk = std::move(fresh);

@@ -51,7 +51,6 @@ struct f5b_vocos {
   std::unique_ptr<WeightStore> ws;
   std::unique_ptr<Arena> wk;
   long long cap_rows = 0;
-  int cap_B = 0;
   WMat embed, head;
   const float *embed_b, *norm_w, *norm_b, *fin_w, *fin_b, *head_b;
   std::vector<VBlock> blocks;
@@ -94,22 +93,24 @@ struct f5b_vocos {
     head_b = W("head.out.bias", V_OUT);
     F5B_CHECK_CUDA(cudaStreamSynchronize(st));
     F5B_CHECK_CUDA(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    lens_dev = warena.alloc_n<int>(kMaxBatch);
   }
   ~f5b_vocos() {
     if (done) cudaEventDestroy(done);
   }
 
+  static constexpr int kMaxBatch = 1 << 16;  // lens_dev is allocated once: a growing batch size must not re-allocate
+
   void ensure(long long rows, int B) {
-    if (wk && rows <= cap_rows && B <= cap_B) return;
+    F5B_REQUIRE(B <= kMaxBatch, "Vocos batch larger than 65536 utterances");
+    if (wk && rows <= cap_rows) return;
     F5B_CHECK_CUDA(cudaDeviceSynchronize());
     const size_t es = ctx.mode == F5B_MODE_BF16 ? 2 : 4;
-    if (wk) rows = rows > cap_rows ? rows : cap_rows, B = B > cap_B ? B : cap_B;
+    rows += rows / 8;  // headroom: slightly larger requests do not re-allocate
     wk.reset();
     cap_rows = 0;
-    cap_B = 0;
     std::unique_ptr<Arena> fresh(new Arena());
     Arena& A = *fresh;
-    lens_dev = A.alloc_n<int>((size_t)B);
     mel_in = A.alloc_n<float>((size_t)rows * V_MEL);
     x0 = A.alloc_n<float>((size_t)rows * V_DIM);
     x = A.alloc_n<float>((size_t)rows * V_DIM);
@@ -118,9 +119,8 @@ struct f5b_vocos {
     a_in = A.alloc((size_t)rows * V_KIN_LD * es);
     norm = A.alloc((size_t)rows * V_DIM * es);
     h = A.alloc((size_t)rows * V_INT * es);
-    wk = std::move(fresh);  // commit: a failed growth leaves no workspace and zero capacities behind
+    wk = std::move(fresh);  // commit: a failed growth leaves no workspace and zero capacity behind
     cap_rows = rows;
-    cap_B = B;
   }
 
   template <typename T>

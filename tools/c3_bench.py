@@ -24,6 +24,9 @@ def main():
     ap.add_argument("--max-batch", type=int, default=64)
     ap.add_argument("--world", type=int, default=1)
     ap.add_argument("--rank", type=int, default=0)
+    ap.add_argument("--batched-vocos", action="store_true", help="one variable-length Vocos call per micro-batch")
+    ap.add_argument("--side-stream", action="store_true", help="run on a torch side stream (as bench.py does)")
+    ap.add_argument("--no-vocos", action="store_true")
     a = ap.parse_args()
     import f5b200
     from f5b200 import _lib as L
@@ -59,10 +62,18 @@ def main():
         b = len(grp)
         mel, _ = cfm.sample(cond=cond, text=text, duration=dur if b > 1 else int(dur[0]), steps=a.nfe, cfg_strength=2.0,
                             sway_sampling_coef=-1.0, y0=y0, return_trajectory=False)
+        if a.no_vocos:
+            return
+        if a.batched_vocos and b > 1:
+            glen = torch.tensor([frames[i] - n_ref for i in grp], dtype=torch.int32, device=dev)
+            voc.decode(mel[:, n_ref:, :].permute(0, 2, 1).contiguous(), glen)
+            return
         for r, i in enumerate(grp):
             voc.decode(mel[r:r + 1, n_ref:frames[i], :].permute(0, 2, 1).contiguous())
 
     data = [inputs(grp) for grp in groups]
+    if a.side_stream:
+        torch.cuda.set_stream(torch.cuda.Stream(dev))
     run(groups[-1], data[-1])  # warm-up: library / module load, allocator
     run(groups[0], data[0])
     torch.cuda.synchronize()

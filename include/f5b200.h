@@ -103,6 +103,23 @@ int f5b_cfm_loss(f5b_plan* plan, const float* x1, const float* x0, const int64_t
                  const int32_t* lens, const uint8_t* span, int32_t B, int32_t N, int32_t nt, int32_t drop_audio_cond,
                  int32_t drop_text, float* loss, float* cond, float* pred, int32_t mem, void* stream);
 
+/* Stage 1 of the training step's backward pass (model/trainer.py:384 `accelerator.backward(loss)` over
+ * CFM.forward, cfm.py:231-302): the loss is differentiated through proj_out, the final AdaLN and the LAST DiTBlock
+ * (dit.py:326-327, modules.py:683-697).  Same inputs as f5b_cfm_loss; each gradient slot names a parameter by its
+ * state-dict name -- transformer_blocks.<depth-1>.{attn_norm.linear, attn.to_q|to_k|to_v|to_out.0, ff.ff.0.0, ff.ff.2}
+ * .{weight,bias}, norm_out.linear.{weight,bias}, proj_out.{weight,bias} -- or "d_block_input" [B, N, dim] (gradient of
+ * the residual stream entering the block) / "pred" [B, N, mel]; other names return F5B_ERR_MISSING.  fp32 CUDA-core
+ * arithmetic in both precision modes.  Synchronous. */
+typedef struct f5b_grad {
+  const char* name;
+  float* data; /* fp32, numel elements, same memory space as the inputs */
+  int64_t numel;
+} f5b_grad;
+int f5b_cfm_loss_tail_grads(f5b_plan* plan, const float* x1, const float* x0, const int64_t* text, const float* time,
+                            const int32_t* lens, const uint8_t* span, int32_t B, int32_t N, int32_t nt,
+                            int32_t drop_audio_cond, int32_t drop_text, float* loss, const f5b_grad* grads,
+                            int32_t n_grads, int32_t mem, void* stream);
+
 /* Replaces MelSpec.forward (model/modules.py:78-104,133-146): wav [B, nw] -> mel [B, 100, nw/256 + 1]. */
 int f5b_mel(const float* wav, int32_t B, int32_t nw, float* mel, int32_t device, int32_t mem, void* stream);
 

@@ -1,0 +1,444 @@
+// Backward kernels of the flow-matching training step (reference src/f5_tts/model/cfm.py:231-302 differentiated by
+// trainer.py:384 `accelerator.backward(loss)`), stage 1: everything needed to push the loss gradient through
+// proj_out, the final AdaLN and one DiTBlock (modules.py:683-697).  fp32 CUDA-core arithmetic: this is the parity
+// tier of the backward pass (checked against torch.autograd over the unmodified reference, tests/test_gpu_backward.py);
+// the tensor-core tier (dgrad / wgrad on tcgen05) is not built yet.  Deterministic: no atomics, fixed reduction order.
+#include "train.h"
+
+namespace f5b {
+
+static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
+
+// ---------------------------------------------------------------------------------------------
+// C[i, j] (+)= sum_k A(i, k) B(k, j) with arbitrary element strides: every dgrad / wgrad form is one call
+//   dX = dY W        : A = dY [M,N] (sa = N,1), B = W [N,K] (sb = K,1)
+//   dW = dY^T X      : A = dY^T    (sa = 1,N), B = X [M,K] (sb = K,1)
+// 64x64x16 tiles, 256 threads, 4x4 per thread.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+sgemm_strided_kernel(const float* __restrict__ A, long long sa0, long long sa1, const float* __restrict__ B,
+                     long long sb0, long long sb1, float* __restrict__ C, long long ldc, int M, int N, int K,
+                     int accumulate) {
+  __shared__ float As[16][64 + 1], Bs[16][64 + 1];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  float acc[4][4] = {};
+  for (int k0 = 0; k0 < K; k0 += 16) {
+    for (int e = tid; e < 64 * 16; e += 256) {
+      // contiguous index first along whichever dimension is unit-stride in memory
+      int i, k;
+      if (sa1 == 1) { k = e & 15; i = e >> 4; } else { i = e & 63; k = e >> 6; }
+      As[k][i] = (m0 + i < M && k0 + k < K) ? A[(long long)(m0 + i) * sa0 + (long long)(k0 + k) * sa1] : 0.0f;
+      int j, kb;
+      if (sb1 == 1) { j = e & 63; kb = e >> 6; } else { kb = e & 15; j = e >> 4; }
+      Bs[kb][j] = (n0 + j < N && k0 + kb < K) ? B[(long long)(k0 + kb) * sb0 + (long long)(n0 + j) * sb1] : 0.0f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[k][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = Bs[k][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int m = m0 + ty * 4 + i, n = n0 + tx * 4 + j;
+      if (m < M && n < N) {
+        float* c = C + (long long)m * ldc + n;
+        *c = accumulate ? *c + acc[i][j] : acc[i][j];
+      }
+    }
+}
+
+void sgemm_strided(cudaStream_t st, const float* A, long long sa0, long long sa1, const float* B, long long sb0,
+                   long long sb1, float* C, long long ldc, int M, int N, int K, bool accumulate) {
+  sgemm_strided_kernel<<<dim3(cdiv(N, 64), cdiv(M, 64)), 256, 0, st>>>(A, sa0, sa1, B, sb0, sb1, C, ldc, M, N, K,
+                                                                          accumulate ? 1 : 0);
+  F5B_POST_LAUNCH();
+}
+
+// out[b, j] = sum over the rows r of batch element b of X[r, j] * (Y ? Y[r, j] : 1); one thread per (b, j), rows in order
+__global__ void __launch_bounds__(256)
+colsum_batch_kernel(const float* __restrict__ X, const float* __restrict__ Y, int rows_per_batch, int cols,
+                    float* __restrict__ out, long long out_bstride) {
+  const int j = blockIdx.x * 256 + threadIdx.x, b = blockIdx.y;
+  if (j >= cols) return;
+  const float* x = X + (long long)b * rows_per_batch * cols + j;
+  const float* y = Y ? Y + (long long)b * rows_per_batch * cols + j : nullptr;
+  float s = 0.0f;
+  for (int r = 0; r < rows_per_batch; ++r) s += y ? x[(long long)r * cols] * y[(long long)r * cols] : x[(long long)r * cols];
+  out[(long long)b * out_bstride + j] = s;
+}
+void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
+                  long long out_bstride) {
+  colsum_batch_kernel<<<dim3(cdiv(cols, 256), batches), 256, 0, st>>>(X, Y, rows_per_batch, cols, out, out_bstride);
+  F5B_POST_LAUNCH();
+}
+
+// ---------------------------------------------------------------------------------------------
+// LayerNorm (no affine, eps) + modulation, forward with saved statistics, and its backward
+//   y = xhat * (1 + scale[b]) + shift[b];   g = dy * (1 + scale[b]);   dx (+)= rstd * (g - mean(g) - xhat * mean(g xhat))
+// one warp per row
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+ln_mod_fwd_save_kernel(const float* __restrict__ x, long long M, int d, const float* __restrict__ scale,
+                       const float* __restrict__ shift, long long vec_bstride, int rows_per_batch, float eps,
+                       float* __restrict__ y, float* __restrict__ xhat, float* __restrict__ rstd_out) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= M) return;
+  const float* xr = x + m * d;
+  float s = 0.0f;
+  for (int c = lane; c < d; c += 32) s += xr[c];
+  const float mean = warp_sum(s) / d;
+  float q = 0.0f;
+  for (int c = lane; c < d; c += 32) {
+    const float t = xr[c] - mean;
+    q += t * t;
+  }
+  const float rstd = rsqrtf(warp_sum(q) / d + eps);
+  const long long b = m / rows_per_batch;
+  const float* sc = scale + b * vec_bstride;
+  const float* sh = shift + b * vec_bstride;
+  for (int c = lane; c < d; c += 32) {
+    const float h = (xr[c] - mean) * rstd;
+    xhat[m * d + c] = h;
+    y[m * d + c] = h * (1.0f + sc[c]) + sh[c];
+  }
+  if (lane == 0) rstd_out[m] = rstd;
+}
+void ln_mod_fwd_save(cudaStream_t st, const float* x, long long M, int d, const float* scale, const float* shift,
+                     long long vec_bstride, int rows_per_batch, float eps, float* y, float* xhat, float* rstd) {
+  ln_mod_fwd_save_kernel<<<cdiv(M, 8), 256, 0, st>>>(x, M, d, scale, shift, vec_bstride, rows_per_batch, eps, y, xhat, rstd);
+  F5B_POST_LAUNCH();
+}
+
+__global__ void __launch_bounds__(256)
+ln_mod_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, const float* __restrict__ rstd,
+                  long long M, int d, const float* __restrict__ scale, long long vec_bstride, int rows_per_batch,
+                  float* __restrict__ dx, int accumulate) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= M) return;
+  const float* sc = scale + (m / rows_per_batch) * vec_bstride;
+  const float* g = dy + m * d;
+  const float* h = xhat + m * d;
+  float s1 = 0.0f, s2 = 0.0f;
+  for (int c = lane; c < d; c += 32) {
+    const float gv = g[c] * (1.0f + sc[c]);
+    s1 += gv;
+    s2 += gv * h[c];
+  }
+  const float m1 = warp_sum(s1) / d, m2 = warp_sum(s2) / d, r = rstd[m];
+  for (int c = lane; c < d; c += 32) {
+    const float v = r * (g[c] * (1.0f + sc[c]) - m1 - h[c] * m2);
+    dx[m * d + c] = accumulate ? dx[m * d + c] + v : v;
+  }
+}
+void ln_mod_bwd(cudaStream_t st, const float* dy, const float* xhat, const float* rstd, long long M, int d,
+                const float* scale, long long vec_bstride, int rows_per_batch, float* dx, bool accumulate) {
+  ln_mod_bwd_kernel<<<cdiv(M, 8), 256, 0, st>>>(dy, xhat, rstd, M, d, scale, vec_bstride, rows_per_batch, dx, accumulate ? 1 : 0);
+  F5B_POST_LAUNCH();
+}
+
+// ---------------------------------------------------------------------------------------------
+// elementwise pieces
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gelu_tanh_fwd_kernel(const float* __restrict__ u, float* __restrict__ h, long long n) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i < n) h[i] = act_apply(ACT_GELU_TANH, u[i]);
+}
+// du = dh * d/du [0.5 u (1 + tanh(k (u + c u^3)))]
+__global__ void __launch_bounds__(256)
+gelu_tanh_bwd_kernel(const float* __restrict__ u, const float* __restrict__ dh, float* __restrict__ du, long long n) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const float x = u[i], k = 0.7978845608028654f, c = 0.044715f;
+  const float t = tanhf(k * (x + c * x * x * x));
+  du[i] = dh[i] * (0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * k * (1.0f + 3.0f * c * x * x));
+}
+void gelu_tanh_fwd(cudaStream_t st, const float* u, float* h, long long n) {
+  gelu_tanh_fwd_kernel<<<cdiv(n, 256), 256, 0, st>>>(u, h, n);
+  F5B_POST_LAUNCH();
+}
+void gelu_tanh_bwd(cudaStream_t st, const float* u, const float* dh, float* du, long long n) {
+  gelu_tanh_bwd_kernel<<<cdiv(n, 256), 256, 0, st>>>(u, dh, du, n);
+  F5B_POST_LAUNCH();
+}
+
+// out[m, :] = v[b(m), :] * x[m, :] (+ bias[:]) ; rows at or beyond row_len[b] give 0 when `zero_dead`
+__global__ void __launch_bounds__(256)
+rowscale_kernel(const float* __restrict__ x, const float* __restrict__ v, long long vec_bstride, int rows_per_batch,
+                const int* __restrict__ row_len, int cols, long long total, float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  const long long m = i / cols;
+  const int c = (int)(i - m * cols);
+  const long long b = m / rows_per_batch;
+  const int pos = (int)(m - b * rows_per_batch);
+  const bool dead = row_len != nullptr && pos >= row_len[b];
+  out[i] = dead ? 0.0f : (v ? v[b * vec_bstride + c] : 1.0f) * x[i];
+}
+void rowscale(cudaStream_t st, const float* x, const float* v, long long vec_bstride, int rows_per_batch,
+              const int* row_len, long long M, int cols, float* out) {
+  rowscale_kernel<<<cdiv(M * cols, 256), 256, 0, st>>>(x, v, vec_bstride, rows_per_batch, row_len, cols, M * cols, out);
+  F5B_POST_LAUNCH();
+}
+
+__global__ void __launch_bounds__(256)
+axpy_kernel(float* __restrict__ y, const float* __restrict__ x, float a, long long n) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i < n) y[i] += a * x[i];
+}
+void axpy(cudaStream_t st, float* y, const float* x, float a, long long n) {
+  axpy_kernel<<<cdiv(n, 256), 256, 0, st>>>(y, x, a, n);
+  F5B_POST_LAUNCH();
+}
+
+__global__ void __launch_bounds__(256)
+add_bias_kernel(float* __restrict__ y, const float* __restrict__ bias, int cols, long long total) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i < total) y[i] += bias[i % cols];
+}
+void add_bias(cudaStream_t st, float* y, const float* bias, long long M, int cols) {
+  add_bias_kernel<<<cdiv(M * cols, 256), 256, 0, st>>>(y, bias, cols, M * cols);
+  F5B_POST_LAUNCH();
+}
+
+// RoPE on the q | k thirds of qkv [M, 3 * inner], interleaved pairs, heads < rope_heads; dir = +1 forward (R x),
+// -1 transpose (R^T x: the backward of the rotation).  cs [rows_per_batch, 64] = (cos_j, sin_j) pairs.
+__global__ void __launch_bounds__(256)
+rope_qk_kernel(float* __restrict__ qkv, long long M, int inner, int rows_per_batch, int rope_heads,
+               const float* __restrict__ cs, float dir) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;  // one thread per (row, q-or-k, pair)
+  const int pairs = inner / 2;
+  if (i >= M * 2 * pairs) return;
+  const long long m = i / (2 * pairs);
+  const int r = (int)(i - m * 2 * pairs), part = r / pairs, p = r - part * pairs;
+  const int col = 2 * p, head = col >> 6;
+  if (head >= rope_heads) return;
+  const int pos = (int)(m % rows_per_batch);
+  const float2 t = *reinterpret_cast<const float2*>(cs + (long long)pos * 64 + (col & 63));
+  float* x = qkv + m * 3 * inner + (long long)part * inner + col;
+  const float a = x[0], c = x[1], sn = dir * t.y;
+  x[0] = a * t.x - c * sn;
+  x[1] = c * t.x + a * sn;
+}
+void rope_qk(cudaStream_t st, float* qkv, long long M, int inner, int rows_per_batch, int rope_heads, const float* cs,
+             float dir) {
+  rope_qk_kernel<<<cdiv(M * inner, 256), 256, 0, st>>>(qkv, M, inner, rows_per_batch, rope_heads, cs, dir);
+  F5B_POST_LAUNCH();
+}
+
+// masked-MSE gradient (cfm.py:298-300): loss = mean over the span frames x mel of (pred - (x1 - x0))^2
+//   dpred = 2 (pred - flow) / count on span rows, 0 elsewhere; count = (#span rows) * mel, counted deterministically
+__global__ void count_span_kernel(const unsigned char* __restrict__ span, long long rows, float* __restrict__ cnt) {
+  __shared__ float part[256];
+  float c = 0.0f;
+  for (long long m = threadIdx.x; m < rows; m += 256) c += span[m] ? 1.0f : 0.0f;
+  part[threadIdx.x] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.0f;
+    for (int i = 0; i < 256; ++i) t += part[i];
+    *cnt = t;
+  }
+}
+__global__ void __launch_bounds__(256)
+mse_grad_kernel(const float* __restrict__ pred, const float* __restrict__ x1, const float* __restrict__ x0,
+                const unsigned char* __restrict__ span, const float* __restrict__ cnt, int mel, long long total,
+                float* __restrict__ dpred) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  const long long m = i / mel;
+  dpred[i] = span[m] ? 2.0f * (pred[i] - (x1[i] - x0[i])) / (*cnt * mel) : 0.0f;
+}
+void mse_grad(cudaStream_t st, const float* pred, const float* x1, const float* x0, const unsigned char* span,
+              long long rows, int mel, float* cnt_scratch, float* dpred) {
+  count_span_kernel<<<1, 256, 0, st>>>(span, rows, cnt_scratch);
+  F5B_POST_LAUNCH();
+  mse_grad_kernel<<<cdiv(rows * mel, 256), 256, 0, st>>>(pred, x1, x0, span, cnt_scratch, mel, rows * mel, dpred);
+  F5B_POST_LAUNCH();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Attention backward (SDPA of modules.py:499-508), fp32, recomputing the probabilities from the saved log-sum-exp:
+//   p_ij = exp(s_ij - lse_i), s_ij = scale q_i.k_j;  D_i = dO_i.O_i;  dS_ij = p_ij (dO_i.v_j - D_i) scale
+//   dq_i = sum_j dS_ij k_j,  dk_j = sum_i dS_ij q_i,  dv_j = sum_i p_ij dO_i
+// One thread owns one query row (lse / dq kernels) or one key row (dk / dv kernels) with its 64-wide vectors in
+// registers; the other side streams through shared memory in tiles of 64 rows.  No atomics.
+// qkv [batches * rows, 3 * inner] (rotated q, k); d_o / o [batches * rows, inner].  Keys j >= kv_len[b] do not exist.
+// ---------------------------------------------------------------------------------------------
+static constexpr int AB_T = 64;  // rows per tile / threads per block
+
+__device__ __forceinline__ void load_tile64(float (*dst)[65], const float* __restrict__ src, long long ld, int r0,
+                                            int rmax) {
+  for (int e = threadIdx.x; e < AB_T * 64; e += AB_T) {
+    const int r = e >> 6, c = e & 63;
+    dst[r][c] = (r0 + r < rmax) ? src[(long long)(r0 + r) * ld + c] : 0.0f;
+  }
+}
+
+// lse_i and D_i
+__global__ void __launch_bounds__(AB_T)
+attn_lse_kernel(const float* __restrict__ qkv, const float* __restrict__ o, const float* __restrict__ d_o, int rows,
+                int heads, const int* __restrict__ kv_len, float scale, float* __restrict__ lse, float* __restrict__ D) {
+  __shared__ float Ks[AB_T][65];
+  const int h = blockIdx.y, b = blockIdx.z, inner = heads * 64;
+  const int i = blockIdx.x * AB_T + threadIdx.x;
+  const int L = kv_len ? kv_len[b] : rows;
+  const float* base = qkv + (long long)b * rows * 3 * inner + h * 64;
+  float q[64];
+  const bool live = i < rows;
+#pragma unroll
+  for (int c = 0; c < 64; ++c) q[c] = live ? base[(long long)i * 3 * inner + c] : 0.0f;
+  float m = -INFINITY, l = 0.0f;
+  for (int j0 = 0; j0 < L; j0 += AB_T) {
+    __syncthreads();
+    load_tile64(Ks, base + inner, 3 * inner, j0, L);
+    __syncthreads();
+    const int nj = min(AB_T, L - j0);
+    for (int j = 0; j < nj; ++j) {
+      float s = 0.0f;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) s = fmaf(q[c], Ks[j][c], s);
+      s *= scale;
+      const float mn = fmaxf(m, s);
+      l = l * expf(m - mn) + expf(s - mn);
+      m = mn;
+    }
+  }
+  if (!live) return;
+  const long long r = (long long)b * rows + i;
+  lse[r * heads + h] = m + logf(l);
+  float dd = 0.0f;
+  const float* op = o + r * inner + h * 64;
+  const float* dp = d_o + r * inner + h * 64;
+#pragma unroll
+  for (int c = 0; c < 64; ++c) dd = fmaf(op[c], dp[c], dd);
+  D[r * heads + h] = dd;
+}
+
+// dq (written into the q third of dqkv)
+__global__ void __launch_bounds__(AB_T)
+attn_dq_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, const float* __restrict__ lse,
+               const float* __restrict__ D, int rows, int heads, const int* __restrict__ kv_len, float scale,
+               float* __restrict__ dqkv) {
+  __shared__ float Ks[AB_T][65], Vs[AB_T][65];
+  const int h = blockIdx.y, b = blockIdx.z, inner = heads * 64;
+  const int i = blockIdx.x * AB_T + threadIdx.x;
+  const int L = kv_len ? kv_len[b] : rows;
+  const float* base = qkv + (long long)b * rows * 3 * inner + h * 64;
+  const bool live = i < rows;
+  const long long r = (long long)b * rows + (live ? i : 0);
+  float q[64], g[64], dq[64];
+#pragma unroll
+  for (int c = 0; c < 64; ++c) {
+    q[c] = live ? base[(long long)i * 3 * inner + c] : 0.0f;
+    g[c] = live ? d_o[r * inner + h * 64 + c] : 0.0f;
+    dq[c] = 0.0f;
+  }
+  const float ls = live ? lse[r * heads + h] : 0.0f, Di = live ? D[r * heads + h] : 0.0f;
+  for (int j0 = 0; j0 < L; j0 += AB_T) {
+    __syncthreads();
+    load_tile64(Ks, base + inner, 3 * inner, j0, L);
+    load_tile64(Vs, base + 2 * inner, 3 * inner, j0, L);
+    __syncthreads();
+    const int nj = min(AB_T, L - j0);
+    for (int j = 0; j < nj; ++j) {
+      float s = 0.0f, dp = 0.0f;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        s = fmaf(q[c], Ks[j][c], s);
+        dp = fmaf(g[c], Vs[j][c], dp);
+      }
+      const float ds = expf(s * scale - ls) * (dp - Di) * scale;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) dq[c] = fmaf(ds, Ks[j][c], dq[c]);
+    }
+  }
+  if (!live) return;
+  float* out = dqkv + r * 3 * inner + h * 64;
+#pragma unroll
+  for (int c = 0; c < 64; ++c) out[c] = dq[c];
+}
+
+// dk (WHICH = 0) or dv (WHICH = 1) of key row j, streaming the query side
+template <int WHICH>
+__global__ void __launch_bounds__(AB_T)
+attn_dkv_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, const float* __restrict__ lse,
+                const float* __restrict__ D, int rows, int heads, const int* __restrict__ kv_len, float scale,
+                float* __restrict__ dqkv) {
+  __shared__ float Qs[AB_T][65], Gs[AB_T][65];
+  __shared__ float Ls[AB_T], Ds[AB_T];
+  const int h = blockIdx.y, b = blockIdx.z, inner = heads * 64;
+  const int j = blockIdx.x * AB_T + threadIdx.x;
+  const int L = kv_len ? kv_len[b] : rows;
+  const float* base = qkv + (long long)b * rows * 3 * inner + h * 64;
+  const bool live = j < L;
+  float k[64], v[64], acc[64];
+#pragma unroll
+  for (int c = 0; c < 64; ++c) {
+    k[c] = live ? base[(long long)j * 3 * inner + inner + c] : 0.0f;
+    v[c] = (WHICH == 0 && live) ? base[(long long)j * 3 * inner + 2 * inner + c] : 0.0f;
+    acc[c] = 0.0f;
+  }
+  for (int i0 = 0; i0 < rows; i0 += AB_T) {
+    __syncthreads();
+    load_tile64(Qs, base, 3 * inner, i0, rows);
+    load_tile64(Gs, d_o + (long long)b * rows * inner + h * 64, inner, i0, rows);
+    if (i0 + (int)threadIdx.x < rows) {
+      Ls[threadIdx.x] = lse[((long long)b * rows + i0 + threadIdx.x) * heads + h];
+      Ds[threadIdx.x] = D[((long long)b * rows + i0 + threadIdx.x) * heads + h];
+    }
+    __syncthreads();
+    const int ni = min(AB_T, rows - i0);
+    for (int i = 0; i < ni; ++i) {
+      float s = 0.0f;
+#pragma unroll
+      for (int c = 0; c < 64; ++c) s = fmaf(Qs[i][c], k[c], s);
+      const float p = expf(s * scale - Ls[i]);
+      if (WHICH == 1) {
+#pragma unroll
+        for (int c = 0; c < 64; ++c) acc[c] = fmaf(p, Gs[i][c], acc[c]);
+      } else {
+        float dp = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 64; ++c) dp = fmaf(Gs[i][c], v[c], dp);
+        const float ds = p * (dp - Ds[i]) * scale;
+#pragma unroll
+        for (int c = 0; c < 64; ++c) acc[c] = fmaf(ds, Qs[i][c], acc[c]);
+      }
+    }
+  }
+  if (j >= rows) return;
+  float* out = dqkv + ((long long)b * rows + j) * 3 * inner + (WHICH == 0 ? inner : 2 * inner) + h * 64;
+#pragma unroll
+  for (int c = 0; c < 64; ++c) out[c] = live ? acc[c] : 0.0f;  // keys beyond kv_len took no part: zero gradient
+}
+
+void attention_backward(cudaStream_t st, const float* qkv, const float* o, const float* d_o, int batches, int rows,
+                        int heads, const int* kv_len, float scale, float* lse, float* D, float* dqkv) {
+  dim3 grid(cdiv(rows, AB_T), heads, batches);
+  attn_lse_kernel<<<grid, AB_T, 0, st>>>(qkv, o, d_o, rows, heads, kv_len, scale, lse, D);
+  F5B_POST_LAUNCH();
+  attn_dq_kernel<<<grid, AB_T, 0, st>>>(qkv, d_o, lse, D, rows, heads, kv_len, scale, dqkv);
+  F5B_POST_LAUNCH();
+  attn_dkv_kernel<0><<<grid, AB_T, 0, st>>>(qkv, d_o, lse, D, rows, heads, kv_len, scale, dqkv);
+  F5B_POST_LAUNCH();
+  attn_dkv_kernel<1><<<grid, AB_T, 0, st>>>(qkv, d_o, lse, D, rows, heads, kv_len, scale, dqkv);
+  F5B_POST_LAUNCH();
+}
+
+}  // namespace f5b

@@ -33,6 +33,10 @@ class Tensor(C.Structure):
     _fields_ = [("name", C.c_char_p), ("data", C.c_void_p), ("numel", C.c_int64), ("on_device", C.c_int32)]
 
 
+class Grad(C.Structure):
+    _fields_ = [("name", C.c_char_p), ("data", C.c_void_p), ("numel", C.c_int64)]
+
+
 _SIGNATURES = {
     "f5b_last_error": (C.c_char_p, []),
     "f5b_version": (C.c_int, []),
@@ -63,6 +67,8 @@ _SIGNATURES = {
     "f5b_op_attention": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                    C.c_int32, C.c_void_p]),
     "f5b_cfm_loss": (C.c_int, [C.c_void_p] * 7 + [C.c_int32] * 5 + [C.c_void_p] * 3 + [C.c_int32, C.c_void_p]),
+    "f5b_cfm_loss_tail_grads": (C.c_int, [C.c_void_p] * 7 + [C.c_int32] * 5 + [C.c_void_p, C.POINTER(Grad), C.c_int32,
+                                                                        C.c_int32, C.c_void_p]),
     "f5b_op_time": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float), C.c_int32,
                               C.c_void_p]),
     "f5b_debug_attn_trace": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32]),

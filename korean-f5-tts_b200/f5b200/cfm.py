@@ -43,14 +43,10 @@ class CFM(nn.Module):
     def device(self):
         return next(self.parameters()).device
 
-    def forward(self, inp, text, *, lens=None, noise_scheduler=None, draws: dict | None = None):
-        """Flow-matching loss of one batch (cfm.py:231-302) -> (loss, cond, pred).
-
-        The random quantities are drawn on the host side in the reference's order and on the reference's devices
-        (`frac_lengths`, the span start, `x0`, `time` on `self.device`; the two drop decisions from `random()`), the rest
-        -- phi, the infilling condition, the backbone evaluation, the masked MSE -- is one `f5b_cfm_loss` call.
-        `draws` (keys frac_lengths, rand, x0, time, drop_audio_cond, drop_text) injects them instead (parity tests).
-        Forward only: the result carries no autograd graph (the backward kernels are not built)."""
+    def _prepare_loss(self, inp, text, lens, draws):
+        """Host half of CFM.forward (cfm.py:231-282): the random draws in the reference's order and on its devices
+        (`frac_lengths`, the span start, `x0`, `time` on `self.device`; the two drop decisions from `random()`), the
+        span mask (model/utils.py:61-77), contiguous fp32 / int tensors for the C ABI."""
         if inp.ndim == 2:  # raw wave (cfm.py:240-243)
             inp = self.mel_spec(inp).permute(0, 2, 1)
             assert inp.shape[-1] == self.num_channels
@@ -79,26 +75,63 @@ class CFM(nn.Module):
             frac_lengths, rand = draws["frac_lengths"].to(dev), draws["rand"].to(dev)
             x0, time = draws["x0"].to(dev, torch.float32), draws["time"].to(dev, torch.float32)
             drop_audio_cond, drop_text = bool(draws["drop_audio_cond"]), bool(draws["drop_text"])
-        # random span to infill (model/utils.py:61-77), clipped to the utterance lengths
         span_len = (frac_lengths * lens).long()
         start = ((lens - span_len) * rand).long().clamp(min=0)
         seq = torch.arange(seq_len, device=dev)
         span = (seq[None, :] >= start[:, None]) & (seq[None, :] < (start + span_len)[:, None]) & mask
+        return dict(x1=inp.contiguous(), x0=x0.contiguous(), tx=text.to(device=dev, dtype=torch.long).contiguous(),
+                    ln=lens.to(torch.int32).contiguous(), sp=span.to(torch.uint8).contiguous(),
+                    t_host=time.detach().to("cpu", torch.float32).contiguous(), batch=batch, seq_len=seq_len,
+                    drop_audio_cond=drop_audio_cond, drop_text=drop_text, dev=dev)
 
-        x1 = inp.contiguous()
-        x0 = x0.contiguous()
-        tx = text.to(device=dev, dtype=torch.long).contiguous()
-        ln = lens.to(torch.int32).contiguous()
-        sp = span.to(torch.uint8).contiguous()
-        t_host = time.detach().to("cpu", torch.float32).contiguous()
+    def forward(self, inp, text, *, lens=None, noise_scheduler=None, draws: dict | None = None):
+        """Flow-matching loss of one batch (cfm.py:231-302) -> (loss, cond, pred): the host draws (`_prepare_loss`), then
+        phi, the infilling condition, the backbone evaluation and the masked MSE in one `f5b_cfm_loss` call.
+        `draws` (keys frac_lengths, rand, x0, time, drop_audio_cond, drop_text) injects the random quantities (parity
+        tests).  The result carries no autograd graph; gradients come from `tail_gradients` (stage 1 of the backward)."""
+        q = self._prepare_loss(inp, text, lens, draws)
+        x1, dev = q["x1"], q["dev"]
         loss = torch.empty((1,), device=dev, dtype=torch.float32)
         cond = torch.empty_like(x1)
         pred = torch.empty_like(x1)
         _lib.check(_lib.lib().f5b_cfm_loss(
-            self.transformer.plan(), x1.data_ptr(), x0.data_ptr(), tx.data_ptr(), t_host.data_ptr(), ln.data_ptr(),
-            sp.data_ptr(), batch, seq_len, tx.shape[1], int(drop_audio_cond), int(drop_text), loss.data_ptr(),
-            cond.data_ptr(), pred.data_ptr(), _lib.mem_kind(x1), _lib.current_stream_ptr(dev)))
+            self.transformer.plan(), x1.data_ptr(), q["x0"].data_ptr(), q["tx"].data_ptr(), q["t_host"].data_ptr(),
+            q["ln"].data_ptr(), q["sp"].data_ptr(), q["batch"], q["seq_len"], q["tx"].shape[1],
+            int(q["drop_audio_cond"]), int(q["drop_text"]), loss.data_ptr(), cond.data_ptr(), pred.data_ptr(),
+            _lib.mem_kind(x1), _lib.current_stream_ptr(dev)))
         return loss[0], cond, pred
+
+    def tail_gradients(self, inp, text, *, lens=None, draws: dict | None = None, names=None):
+        """Stage 1 of the backward pass (trainer.py:384 over CFM.forward): the loss and its gradients with respect to
+        the parameters of proj_out, norm_out and the LAST DiT block -- `{state-dict name: tensor}` with the reference's
+        names (`transformer.` prefix included) -- plus `d_block_input` (gradient of the residual stream entering that
+        block).  One `f5b_cfm_loss_tail_grads` call; fp32 CUDA-core backward arithmetic in both precision modes."""
+        import ctypes as C
+
+        tr = self.transformer
+        q = self._prepare_loss(inp, text, lens, draws)
+        x1, dev = q["x1"], q["dev"]
+        blk = f"transformer_blocks.{tr.depth - 1}"
+        params = dict(tr.named_parameters())
+        if names is None:
+            names = [n for n in params if n.startswith(blk + ".") or n.startswith("norm_out.") or n.startswith("proj_out.")]
+            names.append("d_block_input")
+        out, slots, keep = {}, [], []
+        for n in names:
+            shape = (q["batch"], q["seq_len"], tr.dim) if n == "d_block_input" else \
+                (q["batch"], q["seq_len"], self.num_channels) if n == "pred" else tuple(params[n].shape)
+            g = torch.empty(shape, device=dev, dtype=torch.float32)
+            out[n if n in ("d_block_input", "pred") else "transformer." + n] = g
+            bn = n.encode()
+            keep.append(bn)
+            slots.append(_lib.Grad(bn, g.data_ptr(), g.numel()))
+        arr = (_lib.Grad * len(slots))(*slots)
+        loss = torch.empty((1,), device=dev, dtype=torch.float32)
+        _lib.check(_lib.lib().f5b_cfm_loss_tail_grads(
+            tr.plan(), x1.data_ptr(), q["x0"].data_ptr(), q["tx"].data_ptr(), q["t_host"].data_ptr(), q["ln"].data_ptr(),
+            q["sp"].data_ptr(), q["batch"], q["seq_len"], q["tx"].shape[1], int(q["drop_audio_cond"]),
+            int(q["drop_text"]), loss.data_ptr(), arr, len(slots), _lib.mem_kind(x1), _lib.current_stream_ptr(dev)))
+        return loss[0], out
 
     def prepare_inputs(self, cond, text, duration, *, lens=None, steps=32, sway_sampling_coef=None, seed=None,
                        max_duration=65536, use_epss=True, no_ref_audio=False, duplicate_test=False, t_inter=0.1,

@@ -1,0 +1,79 @@
+"""Stage 1 of the backward pass (reference trainer.py:384 `accelerator.backward(loss)` over
+CFM.forward, cfm.py:231-302): gradients of the last DiTBlock, norm_out and proj_out parameters and of the residual stream
+entering the block, through `f5b_cfm_loss_tail_grads`.
+  * against golden gradients of the UNMODIFIED reference (tests/golden/grads_*.npz, oracle/make_golden_grads.py);
+  * at model width 1024 against torch.autograd over the oracle, in the fp32 and the 16-bit forward modes."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import O, build_cfm, max_abs
+from test_oracle_golden import loss_case
+
+pytestmark = pytest.mark.gpu
+GRAD_CASES = ["dit_v1style_b3_mask", "dit_smallstyle_b2_nomask"]
+
+
+def _draws(d):
+    return dict(frac_lengths=d.frac_lengths, rand=d.rand, x0=d.x0, time=d.time, drop_audio_cond=d.drop_audio_cond,
+                drop_text=d.drop_text)
+
+
+@pytest.mark.parametrize("name", GRAD_CASES)
+def test_tail_gradients_vs_reference_golden(name, golden_dir):
+    cfg, sd, x1, text, lens, _ = loss_case(name, golden_dir)
+    gold = np.load(os.path.join(golden_dir, f"grads_{name}.npz"))
+    d = O.draw_loss_randoms(x1, int(gold["seed"]))
+    cfm = build_cfm(cfg, sd, "fp32")
+    loss, grads = cfm.tail_gradients(x1.cuda(), text.cuda(), lens=lens.cuda(), draws=_draws(d))
+    assert abs(float(loss) - float(gold["loss"])) <= 1e-4 * float(gold["loss"])
+    names = [k for k in gold.files if k not in ("loss", "seed")]
+    assert len(names) == 19 and set(names) == set(grads)  # 18 parameters + d_block_input
+    worst = 0.0
+    for k in names:
+        g, w = grads[k].cpu(), torch.from_numpy(gold[k])
+        if k == "d_block_input":  # frames past an utterance's length carry no defined gradient in either implementation
+            keep = O.lens_to_mask(lens, length=x1.shape[1])[..., None]
+            g, w = g * keep, w * keep
+        assert g.shape == w.shape, k
+        rel = max_abs(g, w) / max(float(w.abs().max()), 1e-8)
+        worst = max(worst, rel)
+        assert rel <= 1e-3, (k, rel)
+    print(f"{name}: 19 gradients vs the reference's autograd, worst max-abs / max|g| = {worst:.2e}")
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("bf16", 3e-2)])
+def test_tail_gradients_vs_oracle_autograd_width_1024(precision, tol):
+    """dim 1024, ragged masked batch: torch.autograd over the oracle's cfm_loss (weights as leaves).  In the 16-bit mode
+    only the forward evaluation feeding the block is 16-bit; the tail is differentiated in fp32."""
+    cfg = O.ArchCfg.named("F5TTS_v1_Base", depth=2, attn_mask_enabled=True)
+    sd = O.synth_backbone_weights(cfg, seed=8)
+    x1, text = O.synth_inputs(160, 160, 30, batch=2, seed=12)
+    lens = torch.tensor([160, 117])
+    d = O.draw_loss_randoms(x1, 31)
+    blk = f"transformer_blocks.{cfg.depth - 1}."
+    leaves = {k: v.clone().requires_grad_(True) for k, v in sd.items()
+              if k.startswith(blk) or k.startswith("norm_out.") or k.startswith("proj_out.")}
+    ref_loss, _, _ = O.cfm_loss({**sd, **leaves}, cfg, x1, text, lens, d)
+    ref_loss.backward()
+    cfm = build_cfm(cfg, sd, precision)
+    loss, grads = cfm.tail_gradients(x1.cuda(), text.cuda(), lens=lens.cuda(), draws=_draws(d))
+    assert abs(float(loss) - float(ref_loss)) <= (1e-4 if precision == "fp32" else 5e-3) * float(ref_loss)
+    worst = 0.0
+    for k, leaf in leaves.items():
+        g = grads["transformer." + k].cpu()
+        rel = max_abs(g, leaf.grad) / max(float(leaf.grad.abs().max()), 1e-8)
+        worst = max(worst, rel)
+        assert rel <= tol, (k, rel)
+    print(f"width 1024 {precision}: {len(leaves)} gradients vs autograd over the oracle, worst relative max-abs {worst:.2e}")
+
+
+def test_unknown_gradient_name_is_loud():
+    cfg = O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2)
+    sd = O.synth_backbone_weights(cfg, seed=3)
+    cfm = build_cfm(cfg, sd, "fp32")
+    x1, text = O.synth_inputs(40, 40, 8, seed=1)
+    with pytest.raises(KeyError):  # only the tail is differentiated so far: anything else must not come back as zeros
+        cfm.tail_gradients(x1.cuda(), text.cuda(), names=["transformer_blocks.0.attn.to_q.weight"])

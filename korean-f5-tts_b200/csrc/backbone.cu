@@ -128,7 +128,7 @@ struct f5b_plan {
   long long last_call_launches = 0;
   bool use_graph = true;
   cudaStream_t own_stream = nullptr;  // used when the caller passes the (uncapturable) legacy default stream
-  float* save_x_last = nullptr;       // backward pass (stage 1): eval() copies the last block's input here
+  float* save_x_last = nullptr;       // backward pass: eval() copies every block's input here ([depth, M, d])
 
   f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, int device);
   ~f5b_plan();
@@ -523,8 +523,8 @@ void f5b_plan::eval(cudaStream_t st, int B, int N, int batches, int tbl_row, int
   std::vector<float*> stack;
   for (int l = 0; l < a.depth; ++l) {
     const Layer& L = layers[l];
-    if (save_x_last != nullptr && l == a.depth - 1) {
-      F5B_CHECK_CUDA(cudaMemcpyAsync(save_x_last, bf.x, (size_t)M * d * 4, cudaMemcpyDeviceToDevice, st));
+    if (save_x_last != nullptr) {
+      F5B_CHECK_CUDA(cudaMemcpyAsync(save_x_last + (size_t)l * M * d, bf.x, (size_t)M * d * 4, cudaMemcpyDeviceToDevice, st));
       count_launch(1);
     }
     const float* ada = is_dit ? bf.ada + (long long)tbl_row * ada_W + (long long)l * 6 * d : nullptr;

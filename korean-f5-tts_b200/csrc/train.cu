@@ -177,6 +177,19 @@ void gelu_tanh_bwd(cudaStream_t st, const float* u, const float* dh, float* du, 
   F5B_POST_LAUNCH();
 }
 
+// dz = dy * d/dz [z sigmoid(z)]
+__global__ void __launch_bounds__(256)
+silu_bwd_kernel(const float* __restrict__ z, const float* __restrict__ dy, float* __restrict__ dz, long long n) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const float s = 1.0f / (1.0f + expf(-z[i]));
+  dz[i] = dy[i] * s * (1.0f + z[i] * (1.0f - s));
+}
+void silu_bwd(cudaStream_t st, const float* z, const float* dy, float* dz, long long n) {
+  silu_bwd_kernel<<<cdiv(n, 256), 256, 0, st>>>(z, dy, dz, n);
+  F5B_POST_LAUNCH();
+}
+
 // out[m, :] = v[b(m), :] * x[m, :] (+ bias[:]) ; rows at or beyond row_len[b] give 0 when `zero_dead`
 __global__ void __launch_bounds__(256)
 rowscale_kernel(const float* __restrict__ x, const float* __restrict__ v, long long vec_bstride, int rows_per_batch,

@@ -16,6 +16,7 @@ void ln_mod_bwd(cudaStream_t st, const float* dy, const float* xhat, const float
                 const float* scale, long long vec_bstride, int rows_per_batch, float* dx, bool accumulate);
 void gelu_tanh_fwd(cudaStream_t st, const float* u, float* h, long long n);
 void gelu_tanh_bwd(cudaStream_t st, const float* u, const float* dh, float* du, long long n);
+void silu_bwd(cudaStream_t st, const float* z, const float* dy, float* dz, long long n);
 void rowscale(cudaStream_t st, const float* x, const float* v, long long vec_bstride, int rows_per_batch,
               const int* row_len, long long M, int cols, float* out);
 void axpy(cudaStream_t st, float* y, const float* x, float a, long long n);

@@ -102,26 +102,27 @@ class CFM(nn.Module):
         return loss[0], cond, pred
 
     def tail_gradients(self, inp, text, *, lens=None, draws: dict | None = None, names=None):
-        """Stage 1 of the backward pass (trainer.py:384 over CFM.forward): the loss and its gradients with respect to
-        the parameters of proj_out, norm_out and the LAST DiT block -- `{state-dict name: tensor}` with the reference's
-        names (`transformer.` prefix included) -- plus `d_block_input` (gradient of the residual stream entering that
-        block).  One `f5b_cfm_loss_tail_grads` call; fp32 CUDA-core backward arithmetic in both precision modes."""
+        """The built part of the backward pass (trainer.py:384 over CFM.forward): the loss and its gradients with respect
+        to the parameters of every DiT block, norm_out, proj_out and the timestep MLP -- `{state-dict name: tensor}` with
+        the reference's names (`transformer.` prefix included) -- plus `d_block_input` / `d_input_embed` (gradient of the
+        residual stream entering the last block / block 0, i.e. what the InputEmbedding backward will consume).  Not yet
+        differentiated: input_embed, text_embed.  One `f5b_cfm_loss_tail_grads` call; fp32 CUDA-core backward arithmetic
+        in both precision modes, blocks recomputed from their saved inputs (activation checkpointing)."""
         import ctypes as C
 
         tr = self.transformer
         q = self._prepare_loss(inp, text, lens, draws)
         x1, dev = q["x1"], q["dev"]
-        blk = f"transformer_blocks.{tr.depth - 1}"
         params = dict(tr.named_parameters())
         if names is None:
-            names = [n for n in params if n.startswith(blk + ".") or n.startswith("norm_out.") or n.startswith("proj_out.")]
-            names.append("d_block_input")
+            names = [n for n in params if n.startswith(("transformer_blocks.", "norm_out.", "proj_out.", "time_embed."))]
+            names += ["d_block_input", "d_input_embed"]
         out, slots, keep = {}, [], []
         for n in names:
-            shape = (q["batch"], q["seq_len"], tr.dim) if n == "d_block_input" else \
+            shape = (q["batch"], q["seq_len"], tr.dim) if n in ("d_block_input", "d_input_embed") else \
                 (q["batch"], q["seq_len"], self.num_channels) if n == "pred" else tuple(params[n].shape)
             g = torch.empty(shape, device=dev, dtype=torch.float32)
-            out[n if n in ("d_block_input", "pred") else "transformer." + n] = g
+            out[n if n in ("d_block_input", "d_input_embed", "pred") else "transformer." + n] = g
             bn = n.encode()
             keep.append(bn)
             slots.append(_lib.Grad(bn, g.data_ptr(), g.numel()))

@@ -1,7 +1,8 @@
 """Golden GRADIENTS of the flow-matching loss from the UNMODIFIED reference: `CFM.forward` (cfm.py:231-302) under the
 seeded draws of oracle/make_golden.py's loss cases, then `loss.backward()` (what trainer.py:384 does), for the
-parameters stage 1 of the B200 backward pass covers -- the last DiTBlock, norm_out, proj_out -- and for the residual
-stream entering that block (captured with a forward pre-hook).
+parameters the B200 backward pass covers: the last DiTBlock, norm_out, proj_out and the residual stream entering that
+block in full; the earlier blocks, the timestep MLP and the residual stream entering block 0 (= InputEmbedding output)
+as every 5th element of the flattened gradient (captured with forward pre-hooks).
 
 Run in the build container (needs /root/reference):  python oracle/make_golden_grads.py
   -> tests/golden/grads_<case>.npz
@@ -19,6 +20,7 @@ from oracle import f5_oracle as O, ref_loader  # noqa: E402
 from oracle.make_golden import build_reference, case_inputs  # noqa: E402
 
 GRAD_CASES = (("dit_v1style_b3_mask", 21), ("dit_smallstyle_b2_nomask", 23))
+SUB = 5
 
 
 def tail_names(depth):
@@ -41,20 +43,33 @@ def main():
             x.retain_grad()
             captured["x"] = x
 
+        def hook0(mod, args, kwargs):
+            x = args[0] if args else kwargs["x"]
+            x.retain_grad()
+            captured["x0"] = x
+
         h = cfm.transformer.transformer_blocks[-1].register_forward_pre_hook(hook, with_kwargs=True)
+        h0 = cfm.transformer.transformer_blocks[0].register_forward_pre_hook(hook0, with_kwargs=True)
         torch.manual_seed(seed)
         random.seed(seed)
         loss, _, pred = cfm(x1, text, lens=lens)
         loss.backward()
         h.remove()
+        h0.remove()
         keep = tail_names(cfg.depth)
         out = {n: p.grad.numpy() for n, p in cfm.named_parameters() if keep(n) and p.grad is not None}
+        # the earlier blocks and the timestep MLP: every SUB-th element of the flattened gradient (keeps the fixture small)
+        for n, p in cfm.named_parameters():
+            if not keep(n) and p.grad is not None and (n.startswith("transformer.transformer_blocks.")
+                                                        or n.startswith("transformer.time_embed.")):
+                out[f"sub{SUB}:" + n] = p.grad.flatten()[::SUB].numpy()
         out["d_block_input"] = captured["x"].grad.numpy()
+        out[f"sub{SUB}:d_input_embed"] = captured["x0"].grad.flatten()[::SUB].numpy()
         out["loss"] = loss.detach().numpy()
         out["seed"] = np.int64(seed)
         path = os.path.join(out_dir, f"grads_{name}.npz")
         np.savez_compressed(path, **out)
-        print(name, "loss", float(loss), len(out) - 3, "parameter gradients,", os.path.getsize(path), "bytes",
+        print(name, "loss", float(loss.detach()), len(out) - 2, "gradients,", os.path.getsize(path), "bytes",
               "max |grad|", max(float(np.abs(v).max()) for k, v in out.items() if k not in ("loss", "seed")))
 
 

@@ -1,6 +1,6 @@
-"""Stage 1 of the backward pass (reference trainer.py:384 `accelerator.backward(loss)` over
-CFM.forward, cfm.py:231-302): gradients of the last DiTBlock, norm_out and proj_out parameters and of the residual stream
-entering the block, through `f5b_cfm_loss_tail_grads`.
+"""The backward pass (reference trainer.py:384 `accelerator.backward(loss)` over CFM.forward,
+cfm.py:231-302): gradients of every DiTBlock, norm_out, proj_out and timestep-MLP parameter and of the residual stream
+entering the last block / block 0, through `f5b_cfm_loss_tail_grads` (input_embed / text_embed: not built yet).
   * against golden gradients of the UNMODIFIED reference (tests/golden/grads_*.npz, oracle/make_golden_grads.py);
   * at model width 1024 against torch.autograd over the oracle, in the fp32 and the 16-bit forward modes."""
 import os
@@ -30,18 +30,21 @@ def test_tail_gradients_vs_reference_golden(name, golden_dir):
     loss, grads = cfm.tail_gradients(x1.cuda(), text.cuda(), lens=lens.cuda(), draws=_draws(d))
     assert abs(float(loss) - float(gold["loss"])) <= 1e-4 * float(gold["loss"])
     names = [k for k in gold.files if k not in ("loss", "seed")]
-    assert len(names) == 19 and set(names) == set(grads)  # 18 parameters + d_block_input
+    # last block + norm_out + proj_out + d_block_input in full; earlier blocks, time_embed, d_input_embed every 5th element
+    assert {k.split(":")[-1] for k in names} == set(grads) and len(names) == 14 * cfg.depth + 4 + 4 + 2
+    keep = O.lens_to_mask(lens, length=x1.shape[1])[..., None]
     worst = 0.0
     for k in names:
-        g, w = grads[k].cpu(), torch.from_numpy(gold[k])
-        if k == "d_block_input":  # frames past an utterance's length carry no defined gradient in either implementation
-            keep = O.lens_to_mask(lens, length=x1.shape[1])[..., None]
-            g, w = g * keep, w * keep
-        assert g.shape == w.shape, k
+        sub = int(k.split(":")[0][3:]) if k.startswith("sub") else 1
+        g, w = grads[k.split(":")[-1]].cpu(), torch.from_numpy(gold[k])
+        if k.endswith(("d_block_input", "d_input_embed")):  # frames past an utterance's length carry no defined gradient
+            g = g * keep
+            w = w * keep if sub == 1 else w * keep.expand_as(g).flatten()[::sub]
+        g = g.flatten()[::sub].reshape(w.shape)
         rel = max_abs(g, w) / max(float(w.abs().max()), 1e-8)
         worst = max(worst, rel)
         assert rel <= 1e-3, (k, rel)
-    print(f"{name}: 19 gradients vs the reference's autograd, worst max-abs / max|g| = {worst:.2e}")
+    print(f"{name}: {len(names)} gradients vs the reference's autograd, worst max-abs / max|g| = {worst:.2e}")
 
 
 @pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("bf16", 3e-2)])
@@ -53,9 +56,8 @@ def test_tail_gradients_vs_oracle_autograd_width_1024(precision, tol):
     x1, text = O.synth_inputs(160, 160, 30, batch=2, seed=12)
     lens = torch.tensor([160, 117])
     d = O.draw_loss_randoms(x1, 31)
-    blk = f"transformer_blocks.{cfg.depth - 1}."
     leaves = {k: v.clone().requires_grad_(True) for k, v in sd.items()
-              if k.startswith(blk) or k.startswith("norm_out.") or k.startswith("proj_out.")}
+              if k.startswith(("transformer_blocks.", "norm_out.", "proj_out.", "time_embed."))}
     ref_loss, _, _ = O.cfm_loss({**sd, **leaves}, cfg, x1, text, lens, d)
     ref_loss.backward()
     cfm = build_cfm(cfg, sd, precision)
@@ -75,5 +77,5 @@ def test_unknown_gradient_name_is_loud():
     sd = O.synth_backbone_weights(cfg, seed=3)
     cfm = build_cfm(cfg, sd, "fp32")
     x1, text = O.synth_inputs(40, 40, 8, seed=1)
-    with pytest.raises(KeyError):  # only the tail is differentiated so far: anything else must not come back as zeros
-        cfm.tail_gradients(x1.cuda(), text.cuda(), names=["transformer_blocks.0.attn.to_q.weight"])
+    with pytest.raises(KeyError):  # not differentiated yet: must not come back as zeros
+        cfm.tail_gradients(x1.cuda(), text.cuda(), names=["input_embed.proj.weight"])

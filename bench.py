@@ -149,8 +149,9 @@ def time_kernel(which: int, M: int, N: int, K: int, iters: int, stream) -> float
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of tc_gemm_kernel from the committed `ncu --set full`
-# capture of a C2 step (profiles/r1_ncu_full_tc_gemm_v5.txt, cold caches): ff1, ff2, qkv, attn_out.
-NCU_TRAFFIC_MB = {"ff1": 8.08, "ff2": 19.63, "qkv": 10.42, "attn_out": 13.68}
+# capture (profiles/r2_ncu_full_tc_gemm.txt: tools/ncu_targets.py gemm, M = 1880, random operands, cold caches).  The
+# residual shapes' reads include the 7.7 MB fp32 tile of the L2 reduce-add target, which is algorithmic.
+NCU_TRAFFIC_MB = {"ff1": 8.08, "ff2": 19.62, "qkv": 10.17, "attn_out": 13.67}
 
 
 def roofline_gemm(stream, pk) -> dict:
@@ -180,7 +181,7 @@ def roofline_gemm(stream, pk) -> dict:
             "peak_source": pk["src"] + " MEASURED_PEAKS.json bf16_tflops (burst: kernel timed alone)",
             "unit": "TFLOP/s", "frac": round(ach / pk["tf"], 4),
             "traffic": round(sum(NCU_TRAFFIC_MB.values()) / 4 * 1e6), "traffic_note":
-            "mean dram read+write bytes per launch over the 4 shapes (ncu --set full, profiles/r1_ncu_full_tc_gemm_v5.txt)",
+            "mean dram read+write bytes per launch over the 4 shapes (ncu --set full, profiles/r2_ncu_full_tc_gemm.txt)",
             "per_shape": per,
             "other_kernels": {
                 "tc_attn_kernel": {"us": round(att_ms * 1e3, 2), "tflops": round(att_f / att_ms / 1e9, 1),

@@ -55,6 +55,7 @@ __global__ void dup_lens_kernel(const int* __restrict__ lens, int B, int batches
 
 struct TextBlock {
   const float *dw_t, *dw_b, *ln_w, *ln_b, *b1, *gamma, *beta, *b2;
+  const float* dw_w = nullptr;  // depthwise weight in the checkpoint's own [td, 1, 7] layout (backward pass)
   WMat pw1, pw2;
 };
 struct Layer {
@@ -105,6 +106,7 @@ struct f5b_plan {
   const float *b_in, *b_out, *tm0_w, *tm0_b, *tm2_w, *tm2_b, *emb_table, *norm_out_g = nullptr;
   const float* conv_b[2];
   const float* conv_w_r[2] = {nullptr, nullptr};
+  const float* conv_w_orig[2] = {nullptr, nullptr};  // [d, d/16, 31] as in the checkpoint (backward pass)
   const __half* conv_w16[2] = {nullptr, nullptr};  // fp16: see input_embed
   float *ada_w = nullptr, *ada_b = nullptr;
   int ada_W = 0;
@@ -190,6 +192,7 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
     dw_transpose<<<(td * 7 + 255) / 256, 256, 0, st>>>(W(p + ".dwconv.weight", (long long)td * 7), dwt, td);
     F5B_POST_LAUNCH();
     tb.dw_t = dwt;
+    tb.dw_w = W(p + ".dwconv.weight", (long long)td * 7);
     tb.dw_b = W(p + ".dwconv.bias", td);
     tb.ln_w = W(p + ".norm.weight", td);
     tb.ln_b = W(p + ".norm.bias", td);
@@ -211,6 +214,7 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
     std::string p = "input_embed.conv_pos_embed.conv1d." + std::to_string(c * 2);
     const float* cw = W(p + ".weight", (long long)d * cg * 31);
     conv_b[c] = W(p + ".bias", d);
+    conv_w_orig[c] = cw;
     long long total = (long long)d * cg * 31;
     if (mode == F5B_MODE_BF16) {
       __half* o = warena.alloc_n<__half>((size_t)total);

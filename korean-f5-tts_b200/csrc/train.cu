@@ -79,8 +79,47 @@ colsum_batch_kernel(const float* __restrict__ X, const float* __restrict__ Y, in
   for (int r = 0; r < rows_per_batch; ++r) s += y ? x[(long long)r * cols] * y[(long long)r * cols] : x[(long long)r * cols];
   out[(long long)b * out_bstride + j] = s;
 }
+// two-level form for one long batch element (the bias / affine gradients sum over ALL rows): chunk sums, then the chunks
+// in order -- still one owner per output, no atomics
+__global__ void __launch_bounds__(256)
+colsum_chunk_kernel(const float* __restrict__ X, const float* __restrict__ Y, int rows, int cols, int chunk,
+                    float* __restrict__ part) {
+  const int j = blockIdx.x * 256 + threadIdx.x, s = blockIdx.y;
+  if (j >= cols) return;
+  const int r0 = s * chunk, r1 = min(rows, r0 + chunk);
+  float acc = 0.0f;
+  for (int r = r0; r < r1; ++r) {
+    const long long i = (long long)r * cols + j;
+    acc += Y ? X[i] * Y[i] : X[i];
+  }
+  part[(long long)s * cols + j] = acc;
+}
+__global__ void __launch_bounds__(256)
+colsum_final_kernel(const float* __restrict__ part, int chunks, int cols, float* __restrict__ out) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= cols) return;
+  float acc = 0.0f;
+  for (int s = 0; s < chunks; ++s) acc += part[(long long)s * cols + j];
+  out[j] = acc;
+}
+static thread_local float* g_colsum_scratch = nullptr;
+static thread_local size_t g_colsum_scratch_floats = 0;
+void colsum_set_scratch(float* p, size_t floats) {
+  g_colsum_scratch = p;
+  g_colsum_scratch_floats = floats;
+}
 void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
                   long long out_bstride) {
+  constexpr int kChunks = 128;
+  if (batches == 1 && rows_per_batch >= 4096 && g_colsum_scratch != nullptr &&
+      (size_t)kChunks * cols <= g_colsum_scratch_floats) {
+    const int chunk = (rows_per_batch + kChunks - 1) / kChunks;
+    colsum_chunk_kernel<<<dim3(cdiv(cols, 256), kChunks), 256, 0, st>>>(X, Y, rows_per_batch, cols, chunk, g_colsum_scratch);
+    F5B_POST_LAUNCH();
+    colsum_final_kernel<<<cdiv(cols, 256), 256, 0, st>>>(g_colsum_scratch, kChunks, cols, out);
+    F5B_POST_LAUNCH();
+    return;
+  }
   colsum_batch_kernel<<<dim3(cdiv(cols, 256), batches), 256, 0, st>>>(X, Y, rows_per_batch, cols, out, out_bstride);
   F5B_POST_LAUNCH();
 }

@@ -10,6 +10,8 @@ void sgemm_strided(cudaStream_t st, const float* A, long long sa0, long long sa1
 // out[b*out_bstride + j] = sum_{r in batch b} X[r,j] * (Y ? Y[r,j] : 1)
 void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
                   long long out_bstride);
+// scratch for the two-level form (>= 128 * cols floats; per calling thread); null switches it off
+void colsum_set_scratch(float* p, size_t floats);
 void ln_mod_fwd_save(cudaStream_t st, const float* x, long long M, int d, const float* scale, const float* shift,
                      long long vec_bstride, int rows_per_batch, float eps, float* y, float* xhat, float* rstd);
 void ln_mod_bwd(cudaStream_t st, const float* dy, const float* xhat, const float* rstd, long long M, int d,
@@ -28,4 +30,28 @@ void mse_grad(cudaStream_t st, const float* pred, const float* x1, const float* 
 void attention_backward(cudaStream_t st, const float* qkv, const float* o, const float* d_o, int batches, int rows,
                         int heads, const int* kv_len, float scale, float* lse, float* D, float* dqkv);
 
+}  // namespace f5b
+
+namespace f5b {
+// embedding stage (train_embed.cu)
+void mish_fwd_mask(cudaStream_t st, const float* z, float* y, int batches, int rows, int cols, const int* row_len);
+void mish_bwd_mask(cudaStream_t st, const float* z, const float* dy, float* dz, int batches, int rows, int cols,
+                   const int* row_len);
+void gelu_erf_fwd(cudaStream_t st, const float* u, float* a, long long n);
+void gelu_erf_bwd(cudaStream_t st, const float* u, const float* da, float* du, long long n);
+void gconv_fwd(cudaStream_t st, const float* x, const float* w, const float* bias, int batches, int rows, int C, int groups,
+               int taps, const int* row_len, float* z);
+void gconv_dgrad(cudaStream_t st, const float* dz, const float* w, int batches, int rows, int C, int groups, int taps,
+                 const int* row_len, float* dx);
+void gconv_wgrad(cudaStream_t st, const float* dz, const float* x, int batches, int rows, int C, int groups, int taps,
+                 const int* row_len, float* dw);
+void grn_fwd(cudaStream_t st, const float* a, int batches, int rows, int C, const int* row_len, const float* gamma,
+             const float* beta, float* stats, float* mu, float* g);
+void grn_bwd(cudaStream_t st, const float* dg, const float* a, int batches, int rows, int C, const int* row_len,
+             const float* gamma, float* stats, const float* mu, float* part, float* da, float* dgamma, float* dbeta);
+void embed_bwd(cudaStream_t st, const float* dte, const long long* text, int B, int nt, int drop_text, int rows, int td,
+               const int* row_len, int mask_padding, int masked_fill_applies, int table_rows, float* dtable);
+void vec_add_const(cudaStream_t st, const float* v, float k, int n, float* out);
+void col_slice(cudaStream_t st, const float* x, long long ldx, int off, int w, long long rows, float* y, long long ldy,
+               int yoff);
 }  // namespace f5b

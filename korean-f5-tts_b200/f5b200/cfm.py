@@ -102,12 +102,11 @@ class CFM(nn.Module):
         return loss[0], cond, pred
 
     def tail_gradients(self, inp, text, *, lens=None, draws: dict | None = None, names=None):
-        """The built part of the backward pass (trainer.py:384 over CFM.forward): the loss and its gradients with respect
-        to the parameters of every DiT block, norm_out, proj_out and the timestep MLP -- `{state-dict name: tensor}` with
-        the reference's names (`transformer.` prefix included) -- plus `d_block_input` / `d_input_embed` (gradient of the
-        residual stream entering the last block / block 0, i.e. what the InputEmbedding backward will consume).  Not yet
-        differentiated: input_embed, text_embed.  One `f5b_cfm_loss_tail_grads` call; fp32 CUDA-core backward arithmetic
-        in both precision modes, blocks recomputed from their saved inputs (activation checkpointing)."""
+        """The backward pass (trainer.py:384 over CFM.forward): the loss and its gradients with respect to EVERY parameter
+        of the DiT -- `{state-dict name: tensor}` with the reference's names (`transformer.` prefix included) -- plus
+        `d_block_input` / `d_input_embed` (gradient of the residual stream entering the last block / block 0).  One
+        `f5b_cfm_loss_tail_grads` call; fp32 CUDA-core backward arithmetic in both precision modes, blocks recomputed
+        from their saved inputs (activation checkpointing); dropout is not modelled (eval-mode function)."""
         import ctypes as C
 
         tr = self.transformer
@@ -115,7 +114,7 @@ class CFM(nn.Module):
         x1, dev = q["x1"], q["dev"]
         params = dict(tr.named_parameters())
         if names is None:
-            names = [n for n in params if n.startswith(("transformer_blocks.", "norm_out.", "proj_out.", "time_embed."))]
+            names = list(params)  # every parameter of the DiT
             names += ["d_block_input", "d_input_embed"]
         out, slots, keep = {}, [], []
         for n in names:

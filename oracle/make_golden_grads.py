@@ -1,7 +1,7 @@
 """Golden GRADIENTS of the flow-matching loss from the UNMODIFIED reference: `CFM.forward` (cfm.py:231-302) under the
 seeded draws of oracle/make_golden.py's loss cases, then `loss.backward()` (what trainer.py:384 does), for the
 parameters the B200 backward pass covers: the last DiTBlock, norm_out, proj_out and the residual stream entering that
-block in full; the earlier blocks, the timestep MLP and the residual stream entering block 0 (= InputEmbedding output)
+block in full; every other parameter (earlier blocks, timestep MLP, input_embed, text_embed) and the residual stream entering block 0
 as every 5th element of the flattened gradient (captured with forward pre-hooks).
 
 Run in the build container (needs /root/reference):  python oracle/make_golden_grads.py
@@ -60,8 +60,7 @@ def main():
         out = {n: p.grad.numpy() for n, p in cfm.named_parameters() if keep(n) and p.grad is not None}
         # the earlier blocks and the timestep MLP: every SUB-th element of the flattened gradient (keeps the fixture small)
         for n, p in cfm.named_parameters():
-            if not keep(n) and p.grad is not None and (n.startswith("transformer.transformer_blocks.")
-                                                        or n.startswith("transformer.time_embed.")):
+            if not keep(n) and p.grad is not None and n.startswith("transformer."):
                 out[f"sub{SUB}:" + n] = p.grad.flatten()[::SUB].numpy()
         out["d_block_input"] = captured["x"].grad.numpy()
         out[f"sub{SUB}:d_input_embed"] = captured["x0"].grad.flatten()[::SUB].numpy()

@@ -1,6 +1,7 @@
 """The backward pass (reference trainer.py:384 `accelerator.backward(loss)` over CFM.forward,
-cfm.py:231-302): gradients of every DiTBlock, norm_out, proj_out and timestep-MLP parameter and of the residual stream
-entering the last block / block 0, through `f5b_cfm_loss_tail_grads` (input_embed / text_embed: not built yet).
+cfm.py:231-302): gradients of EVERY parameter of the DiT (blocks, norm_out, proj_out, timestep MLP, input embedding with
+its grouped convolutions, text embedding with its ConvNeXt-V2 / GRN blocks) and of the residual stream entering the last
+block / block 0, through `f5b_cfm_loss_tail_grads`.
   * against golden gradients of the UNMODIFIED reference (tests/golden/grads_*.npz, oracle/make_golden_grads.py);
   * at model width 1024 against torch.autograd over the oracle, in the fp32 and the 16-bit forward modes."""
 import os
@@ -31,7 +32,8 @@ def test_tail_gradients_vs_reference_golden(name, golden_dir):
     assert abs(float(loss) - float(gold["loss"])) <= 1e-4 * float(gold["loss"])
     names = [k for k in gold.files if k not in ("loss", "seed")]
     # last block + norm_out + proj_out + d_block_input in full; earlier blocks, time_embed, d_input_embed every 5th element
-    assert {k.split(":")[-1] for k in names} == set(grads) and len(names) == 14 * cfg.depth + 4 + 4 + 2
+    assert {k.split(":")[-1] for k in names} == set(grads)  # every DiT parameter + the two stream gradients
+    assert len(names) == 14 * cfg.depth + 4 + 4 + 6 + 1 + 10 * cfg.conv_layers + 2
     keep = O.lens_to_mask(lens, length=x1.shape[1])[..., None]
     worst = 0.0
     for k in names:
@@ -56,8 +58,7 @@ def test_tail_gradients_vs_oracle_autograd_width_1024(precision, tol):
     x1, text = O.synth_inputs(160, 160, 30, batch=2, seed=12)
     lens = torch.tensor([160, 117])
     d = O.draw_loss_randoms(x1, 31)
-    leaves = {k: v.clone().requires_grad_(True) for k, v in sd.items()
-              if k.startswith(("transformer_blocks.", "norm_out.", "proj_out.", "time_embed."))}
+    leaves = {k: v.clone().requires_grad_(True) for k, v in sd.items()}  # every parameter of the DiT
     ref_loss, _, _ = O.cfm_loss({**sd, **leaves}, cfg, x1, text, lens, d)
     ref_loss.backward()
     cfm = build_cfm(cfg, sd, precision)
@@ -77,5 +78,5 @@ def test_unknown_gradient_name_is_loud():
     sd = O.synth_backbone_weights(cfg, seed=3)
     cfm = build_cfm(cfg, sd, "fp32")
     x1, text = O.synth_inputs(40, 40, 8, seed=1)
-    with pytest.raises(KeyError):  # not differentiated yet: must not come back as zeros
-        cfm.tail_gradients(x1.cuda(), text.cuda(), names=["input_embed.proj.weight"])
+    with pytest.raises(KeyError):  # a name that is no parameter must not come back as zeros
+        cfm.tail_gradients(x1.cuda(), text.cuda(), names=["input_embed.proj.weights"])

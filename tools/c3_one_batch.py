@@ -17,7 +17,8 @@ def main():
     steps = int(os.environ.get("STEPS", "2"))
     dev = torch.device("cuda", 0)
     bench.V1_BASE["attn_mask_enabled"] = True
-    dit, _ = bench.synth_state(0)
+    dit, voc = bench.synth_state(0)
+    voc = voc.to(dev).eval()
     cfm = f5b200.CFM(transformer=dit.to(dev), mel_spec_kwargs=dict(mel_spec_type="vocos")).eval()
     g = torch.Generator().manual_seed(0)
     b = 16
@@ -30,6 +31,13 @@ def main():
     for _ in range(int(os.environ.get("REPS", "1"))):
         cfm.sample(cond=cond, text=text, duration=durs.to(dev), steps=steps, cfg_strength=2.0, sway_sampling_coef=-1.0,
                    y0=y0, return_trajectory=False)
+        # the memory-bound tail of the path at the same batch size: Vocos (dwconv + LN, fused iSTFT / overlap-add) over the
+        # generated frames with per-row lengths, and the mel front end over 16 x 20 s of audio
+        glen = (durs - 282).to(torch.int32).to(dev)
+        mel = (torch.randn(b, 100, n - 282, generator=g) * 2 - 3).clamp(min=-11.5).to(dev)
+        voc.decode(mel, glen)
+        wav = (torch.randn(b, 20 * 24000, generator=g) * 0.1).to(dev)
+        cfm.mel_spec(wav)
     torch.cuda.synchronize()
     print("ok", b, n)
 

@@ -120,6 +120,15 @@ int f5b_cfm_loss_tail_grads(f5b_plan* plan, const float* x1, const float* x0, co
                             int32_t drop_audio_cond, int32_t drop_text, float* loss, const f5b_grad* grads,
                             int32_t n_grads, int32_t mem, void* stream);
 
+/* Optimiser step of the training loop over FLAT fp32 device buffers (model/trainer.py:118-131 AdamW with
+ * torch.optim.AdamW semantics, :387 clip_grad_norm_, :395 EMA): f5b_op_sumsq gives the squared gradient norm (double,
+ * fixed reduction tree; scratch >= 1024 doubles), f5b_op_adamw applies one update, reading the gradient as
+ * grad * grad_scale (data-parallel average x clip coefficient) and optionally refreshing an EMA copy.  Asynchronous. */
+int f5b_op_sumsq(const float* x, int64_t n, double* scratch, double* out, int32_t device, void* stream);
+int f5b_op_adamw(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, float* ema, int64_t n, float lr,
+                 float beta1, float beta2, float eps, float weight_decay, int32_t step, float grad_scale,
+                 float ema_decay, int32_t device, void* stream);
+
 /* Replaces MelSpec.forward (model/modules.py:78-104,133-146): wav [B, nw] -> mel [B, 100, nw/256 + 1]. */
 int f5b_mel(const float* wav, int32_t B, int32_t nw, float* mel, int32_t device, int32_t mem, void* stream);
 

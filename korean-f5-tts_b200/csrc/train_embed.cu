@@ -149,8 +149,52 @@ gconv_wgrad_kernel(const float* __restrict__ dz, const float* __restrict__ x, in
   }
   dw[i] = acc;
 }
+// 64 channels per group (dim 1024): one CTA per (group, tap) accumulates its 64 x 64 block of dw over all rows through
+// shared-memory tiles of 16 rows -- 4 x 4 outputs per thread instead of one thread per weight walking every row
+__global__ void __launch_bounds__(256)
+gconv_wgrad64_kernel(const float* __restrict__ dz, const float* __restrict__ x, int batches, int rows, int C, int taps,
+                     const int* __restrict__ row_len, float* __restrict__ dw) {
+  __shared__ float Gs[16][64 + 1], Xs[16][64 + 1];
+  const int g = blockIdx.x, tap = blockIdx.y, pad = taps / 2;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  float acc[4][4] = {};
+  for (int b = 0; b < batches; ++b) {
+    const int len = row_len ? row_len[b] : rows;
+    for (int t0 = 0; t0 < rows; t0 += 16) {
+      for (int e = tid; e < 16 * 64; e += 256) {
+        const int r = e >> 6, c = e & 63, t = t0 + r, tt = t + tap - pad;
+        Gs[r][c] = t < rows ? dz[((long long)b * rows + t) * C + g * 64 + c] : 0.0f;
+        Xs[r][c] = (t < rows && tt >= 0 && tt < len) ? x[((long long)b * rows + tt) * C + g * 64 + c] : 0.0f;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int r = 0; r < 16; ++r) {
+        float a[4], v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = Gs[r][ty * 4 + i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = Xs[r][tx * 4 + j];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], v[j], acc[i][j]);
+      }
+      __syncthreads();
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      dw[((long long)(g * 64 + ty * 4 + i) * 64 + tx * 4 + j) * taps + tap] = acc[i][j];
+}
 void gconv_wgrad(cudaStream_t st, const float* dz, const float* x, int batches, int rows, int C, int groups, int taps,
                  const int* row_len, float* dw) {
+  if (C / groups == 64) {
+    gconv_wgrad64_kernel<<<dim3(groups, taps), 256, 0, st>>>(dz, x, batches, rows, C, taps, row_len, dw);
+    F5B_POST_LAUNCH();
+    return;
+  }
   const long long total = (long long)C * (C / groups) * taps;
   gconv_wgrad_kernel<<<cdiv2(total, 256), 256, 0, st>>>(dz, x, batches, rows, C, C / groups, taps, row_len, total, dw);
   F5B_POST_LAUNCH();

@@ -13,6 +13,7 @@ from .infer import infer_batch_process  # noqa: F401
 from .checkpoint import get_tokenizer, load_checkpoint, load_model  # noqa: F401
 from .api import F5TTS, chunk_text, infer_process  # noqa: F401
 from . import serving  # noqa: F401
+from .train import TrainStep  # noqa: F401
 
 __all__ = ["CFM", "DiT", "UNetT", "MelSpec", "Vocos", "load_vocoder", "lens_to_mask", "list_str_to_idx",
            "list_str_to_tensor", "get_epss_timesteps", "sway_time_grid", "seed_everything", "F5BError", "infer_batch_process",

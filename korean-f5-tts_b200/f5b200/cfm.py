@@ -101,12 +101,13 @@ class CFM(nn.Module):
             _lib.mem_kind(x1), _lib.current_stream_ptr(dev)))
         return loss[0], cond, pred
 
-    def tail_gradients(self, inp, text, *, lens=None, draws: dict | None = None, names=None):
+    def tail_gradients(self, inp, text, *, lens=None, draws: dict | None = None, names=None, buffers: dict | None = None):
         """The backward pass (trainer.py:384 over CFM.forward): the loss and its gradients with respect to EVERY parameter
         of the DiT -- `{state-dict name: tensor}` with the reference's names (`transformer.` prefix included) -- plus
         `d_block_input` / `d_input_embed` (gradient of the residual stream entering the last block / block 0).  One
         `f5b_cfm_loss_tail_grads` call; fp32 CUDA-core backward arithmetic in both precision modes, blocks recomputed
-        from their saved inputs (activation checkpointing); dropout is not modelled (eval-mode function)."""
+        from their saved inputs (activation checkpointing); dropout is not modelled (eval-mode function).  `buffers`
+        ({name: preallocated fp32 tensor}) receives the gradients in place (the training step's flat gradient buffer)."""
         import ctypes as C
 
         tr = self.transformer
@@ -120,7 +121,8 @@ class CFM(nn.Module):
         for n in names:
             shape = (q["batch"], q["seq_len"], tr.dim) if n in ("d_block_input", "d_input_embed") else \
                 (q["batch"], q["seq_len"], self.num_channels) if n == "pred" else tuple(params[n].shape)
-            g = torch.empty(shape, device=dev, dtype=torch.float32)
+            g = buffers[n] if buffers is not None and n in buffers else torch.empty(shape, device=dev, dtype=torch.float32)
+            assert tuple(g.shape) == tuple(shape) and g.is_contiguous() and g.dtype == torch.float32, n
             out[n if n in ("d_block_input", "d_input_embed", "pred") else "transformer." + n] = g
             bn = n.encode()
             keep.append(bn)

@@ -80,3 +80,37 @@ def test_unknown_gradient_name_is_loud():
     x1, text = O.synth_inputs(40, 40, 8, seed=1)
     with pytest.raises(KeyError):  # a name that is no parameter must not come back as zeros
         cfm.tail_gradients(x1.cuda(), text.cuda(), names=["input_embed.proj.weights"])
+
+
+def test_train_step_matches_torch_adamw_on_the_oracle():
+    """Two optimiser steps of `TrainStep` (backward + global-norm clip + AdamW, flat buffers) against torch.optim.AdamW +
+    clip_grad_norm_ driven by autograd over the oracle with the same draws (reference trainer.py:146,384-390)."""
+    import f5b200
+
+    cfg = O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2, attn_mask_enabled=True)
+    sd = O.synth_backbone_weights(cfg, seed=5)
+    x1, text = O.synth_inputs(60, 60, 12, batch=2, seed=3)
+    lens = torch.tensor([60, 44])
+    cfm = build_cfm(cfg, sd, "fp32")
+    ts = f5b200.TrainStep(cfm, lr=1e-3, weight_decay=1e-2, max_grad_norm=0.05, ema_decay=0.9)
+    leaves = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    opt = torch.optim.AdamW(list(leaves.values()), lr=1e-3, weight_decay=1e-2)
+    ema = {k: v.detach().clone() for k, v in leaves.items()}
+    for it in range(2):
+        d = O.draw_loss_randoms(x1, 40 + it)
+        loss = ts.step(x1.cuda(), text.cuda(), lens=lens.cuda(), draws=_draws(d))
+        opt.zero_grad()
+        ref_loss, _, _ = O.cfm_loss(leaves, cfg, x1, text, lens, d)
+        ref_loss.backward()
+        norm = torch.nn.utils.clip_grad_norm_(list(leaves.values()), 0.05)
+        opt.step()
+        for k in ema:
+            ema[k] = 0.9 * ema[k] + 0.1 * leaves[k].detach()
+        assert abs(float(loss) - float(ref_loss.detach())) <= 1e-4 * float(ref_loss.detach())
+        assert abs(ts.last["grad_norm"] - float(norm)) <= 1e-4 * float(norm) and ts.last["clip_coef"] < 1.0
+    got = cfm.transformer.state_dict()
+    worst = max(max_abs(got[k], v.detach()) / max(float(v.detach().abs().max()), 1e-8) for k, v in leaves.items())
+    e = ts.ema_state_dict()
+    worst_ema = max(max_abs(e["ema_model.transformer." + k], v) / max(float(v.abs().max()), 1e-8) for k, v in ema.items())
+    print(f"two AdamW steps: parameters within {worst:.2e}, EMA within {worst_ema:.2e} (relative to max|w|) of torch.optim.AdamW")
+    assert worst <= 1e-4 and worst_ema <= 1e-4

@@ -482,6 +482,65 @@ def run_c4(voc, dev, stream, pk: dict, steps: int = 3, warmup: int = 2) -> dict:
             "tflops": round(fl / (ms / 1e3) / 1e12, 1), "frac_of_sustained_peak": round(fl / (ms / 1e3) / 1e12 / pk["tf_sus"], 4)}
 
 
+# ---- C5: data-parallel training step (BASELINE.json configs[4]) ------------------------------------------------------
+C5_BATCH, C5_FRAMES = 40, 960  # 38 400 frames per GPU per step (configs/F5TTS_v1_Base.yaml:7 batch_size_per_gpu)
+
+
+def run_c5(dev, stream, rank: int, world: int, pk: dict, steps: int = 2, warmup: int = 1) -> dict:
+    """F5TTS_v1_Base training step, WEAK scaling (38 400 frames per GPU, trainer.py:59-70 DDP): 16-bit tensor-core forward,
+    backward of every parameter (GEMMs and grouped convolutions on tcgen05 with bf16 operands, attention backward still
+    on the CUDA cores), ONE NCCL all-reduce of the 1.34 GB fp32 gradient over NVLink, global-norm clip, fused AdamW.
+    Timed per step with CUDA events, max over ranks; the all-reduce is timed on its own as well."""
+    import torch.distributed as dist
+
+    import f5b200
+
+    dit, _ = synth_state(0)  # same initial weights on every rank (what DDP's broadcast establishes)
+    cfm = f5b200.CFM(transformer=dit.to(dev), mel_spec_kwargs=dict(mel_spec_type="vocos")).eval()
+    ts = f5b200.TrainStep(cfm, lr=7.5e-5, max_grad_norm=1.0)
+    g = torch.Generator().manual_seed(100 + rank)
+    x1 = (torch.randn(C5_BATCH, C5_FRAMES, 100, generator=g) * 2 - 3).clamp(min=-11.5).to(dev)
+    text = torch.randint(0, 58, (C5_BATCH, N_TEXT), generator=g).to(dev)
+    lens = torch.full((C5_BATCH,), C5_FRAMES, device=dev)
+    times, ar, losses = [], [], []
+    with torch.cuda.stream(stream):
+        for i in range(warmup + steps):
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            loss = ts.step(x1, text, lens=lens)
+            cfm.transformer.plan()  # the next step's packed 16-bit weights belong to this step's cost
+            e1.record(stream)
+            torch.cuda.synchronize(dev)
+            if i >= warmup:
+                times.append(e0.elapsed_time(e1))
+                ar.append(ts.timings_ms()["allreduce_ms"])
+            losses.append(float(loss))
+    t = torch.tensor([sum(times) / len(times), sum(ar) / len(ar)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ar_ms = float(t[0]), float(t[1])
+    assert all(l == l for l in losses) and losses[-1] < losses[0], f"training loss did not decrease: {losses}"
+    fwd = flops_per_eval(n=C5_FRAMES, branches=1) * C5_BATCH
+    nparam = ts.flat_param.numel()
+    del ts, cfm, dit
+    torch.cuda.empty_cache()
+    return {"workload": f"C5: {MODEL} training step, {C5_BATCH} x {C5_FRAMES} = {C5_BATCH * C5_FRAMES} frames per GPU, "
+                        f"random-span flow-matching loss, backward of all {nparam / 1e6:.1f} M parameters, all-reduce + "
+                        f"clip + AdamW; x{world} data parallel; {steps} timed steps after {warmup} warm-up",
+            "scaling": "weak", "ms_per_step": round(ms, 1),
+            "frames_per_s": round(world * C5_BATCH * C5_FRAMES / (ms / 1e3), 1),
+            "tflops_per_gpu": round(3 * fwd / (ms / 1e3) / 1e12, 1),
+            "frac_of_sustained_peak": round(3 * fwd / (ms / 1e3) / 1e12 / pk["tf_sus"], 4),
+            "allreduce_ms": round(ar_ms, 3), "allreduce_bytes": nparam * 4,
+            "allreduce_busbw_GBps": round(2 * (world - 1) / world * nparam * 4 / (ar_ms / 1e3) / 1e9, 1) if world > 1 else None,
+            "loss_first_last": [round(losses[0], 4), round(losses[-1], 4)],
+            "note": "the attention backward runs on the CUDA cores (fp32) and is about half of the step; fp32 master "
+                    "weights / gradients / Adam moments; the all-reduce is not overlapped with the backward yet"}
+
+
 # ---- our arm -------------------------------------------------------------------------------------------------------
 MEL_TOL_16BIT = 2e-2  # north star: 16-bit mode mel within 2e-2 max-abs of the fp32 reference
 
@@ -599,6 +658,11 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     if rank == 0 and world == 1 and not args.no_c4:
         dit.invalidate_plan()  # release the C2 / C3 plan's workspace first
         c4 = run_c4(voc, dev, stream, pk)
+    c5 = None
+    if not args.no_c5:
+        dit.invalidate_plan()
+        torch.cuda.empty_cache()
+        c5 = run_c5(dev, stream, rank, world, pk)
     if rank != 0:
         return
     ms_step = ms_total / args.steps
@@ -617,7 +681,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
             "step_tflops": {"achieved": round(step_tf, 1), "peak_sustained": pk["tf_sus"],
                             "frac": round(step_tf / pk["tf_sus"], 4),
                             "flops_per_step": NFE * flops_per_eval() + 27.0e6 * GEN_FRAMES},
-            "roofline": roof, "c3": c3, "c4": c4, "f4_streaming": f4}
+            "roofline": roof, "c3": c3, "c4": c4, "c5": c5, "f4_streaming": f4}
     if world == 1 and not args.no_cpu:
         state = {k: v.detach().float().cpu() for k, v in dit.state_dict().items()}
         vstate = {k: v.detach().float().cpu() for k, v in voc.state_dict().items()}
@@ -635,6 +699,7 @@ def main():
     ap.add_argument("--no-c1", action="store_true", help="reference arm: skip the C1 (F5TTS_Small) CPU run")
     ap.add_argument("--no-c3", action="store_true", help="skip the C3 record (256 utterances, sharded over the ranks)")
     ap.add_argument("--no-c4", action="store_true", help="skip the C4 record (E2TTS_Base 30 s, N=1 only)")
+    ap.add_argument("--no-c5", action="store_true", help="skip the C5 record (data-parallel training step)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -334,7 +334,7 @@ void mse_grad(cudaStream_t st, const float* pred, const float* x1, const float* 
 // ---------------------------------------------------------------------------------------------
 static constexpr int AB_T = 64;  // rows per tile / threads per block
 
-__device__ __forceinline__ void load_tile64(float (*dst)[65], const float* __restrict__ src, long long ld, int r0,
+__device__ __forceinline__ void load_tile64(float (*dst)[64], const float* __restrict__ src, long long ld, int r0,
                                             int rmax) {
   for (int e = threadIdx.x; e < AB_T * 64; e += AB_T) {
     const int r = e >> 6, c = e & 63;
@@ -346,7 +346,7 @@ __device__ __forceinline__ void load_tile64(float (*dst)[65], const float* __res
 __global__ void __launch_bounds__(AB_T)
 attn_lse_kernel(const float* __restrict__ qkv, const float* __restrict__ o, const float* __restrict__ d_o, int rows,
                 int heads, const int* __restrict__ kv_len, float scale, float* __restrict__ lse, float* __restrict__ D) {
-  __shared__ float Ks[AB_T][65];
+  __shared__ __align__(16) float Ks[AB_T][64];
   const int h = blockIdx.y, b = blockIdx.z, inner = heads * 64;
   const int i = blockIdx.x * AB_T + threadIdx.x;
   const int L = kv_len ? kv_len[b] : rows;
@@ -364,7 +364,10 @@ attn_lse_kernel(const float* __restrict__ qkv, const float* __restrict__ o, cons
     for (int j = 0; j < nj; ++j) {
       float s = 0.0f;
 #pragma unroll
-      for (int c = 0; c < 64; ++c) s = fmaf(q[c], Ks[j][c], s);
+      for (int c = 0; c < 64; c += 4) {  // one 16-byte broadcast read per four FMAs
+        const float4 kv = *reinterpret_cast<const float4*>(&Ks[j][c]);
+        s = fmaf(q[c], kv.x, s); s = fmaf(q[c + 1], kv.y, s); s = fmaf(q[c + 2], kv.z, s); s = fmaf(q[c + 3], kv.w, s);
+      }
       s *= scale;
       const float mn = fmaxf(m, s);
       l = l * expf(m - mn) + expf(s - mn);
@@ -387,7 +390,7 @@ __global__ void __launch_bounds__(AB_T)
 attn_dq_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, const float* __restrict__ lse,
                const float* __restrict__ D, int rows, int heads, const int* __restrict__ kv_len, float scale,
                float* __restrict__ dqkv) {
-  __shared__ float Ks[AB_T][65], Vs[AB_T][65];
+  __shared__ __align__(16) float Ks[AB_T][64], Vs[AB_T][64];
   const int h = blockIdx.y, b = blockIdx.z, inner = heads * 64;
   const int i = blockIdx.x * AB_T + threadIdx.x;
   const int L = kv_len ? kv_len[b] : rows;
@@ -411,13 +414,19 @@ attn_dq_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, con
     for (int j = 0; j < nj; ++j) {
       float s = 0.0f, dp = 0.0f;
 #pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        s = fmaf(q[c], Ks[j][c], s);
-        dp = fmaf(g[c], Vs[j][c], dp);
+      for (int c = 0; c < 64; c += 4) {
+        const float4 kv = *reinterpret_cast<const float4*>(&Ks[j][c]);
+        const float4 vv = *reinterpret_cast<const float4*>(&Vs[j][c]);
+        s = fmaf(q[c], kv.x, s); s = fmaf(q[c + 1], kv.y, s); s = fmaf(q[c + 2], kv.z, s); s = fmaf(q[c + 3], kv.w, s);
+        dp = fmaf(g[c], vv.x, dp); dp = fmaf(g[c + 1], vv.y, dp); dp = fmaf(g[c + 2], vv.z, dp); dp = fmaf(g[c + 3], vv.w, dp);
       }
       const float ds = expf(s * scale - ls) * (dp - Di) * scale;
 #pragma unroll
-      for (int c = 0; c < 64; ++c) dq[c] = fmaf(ds, Ks[j][c], dq[c]);
+      for (int c = 0; c < 64; c += 4) {
+        const float4 kv = *reinterpret_cast<const float4*>(&Ks[j][c]);
+        dq[c] = fmaf(ds, kv.x, dq[c]); dq[c + 1] = fmaf(ds, kv.y, dq[c + 1]);
+        dq[c + 2] = fmaf(ds, kv.z, dq[c + 2]); dq[c + 3] = fmaf(ds, kv.w, dq[c + 3]);
+      }
     }
   }
   if (!live) return;
@@ -432,7 +441,7 @@ __global__ void __launch_bounds__(AB_T)
 attn_dkv_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, const float* __restrict__ lse,
                 const float* __restrict__ D, int rows, int heads, const int* __restrict__ kv_len, float scale,
                 float* __restrict__ dqkv) {
-  __shared__ float Qs[AB_T][65], Gs[AB_T][65];
+  __shared__ __align__(16) float Qs[AB_T][64], Gs[AB_T][64];
   __shared__ float Ls[AB_T], Ds[AB_T];
   const int h = blockIdx.y, b = blockIdx.z, inner = heads * 64;
   const int j = blockIdx.x * AB_T + threadIdx.x;
@@ -459,18 +468,32 @@ attn_dkv_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, co
     for (int i = 0; i < ni; ++i) {
       float s = 0.0f;
 #pragma unroll
-      for (int c = 0; c < 64; ++c) s = fmaf(Qs[i][c], k[c], s);
+      for (int c = 0; c < 64; c += 4) {
+        const float4 qv = *reinterpret_cast<const float4*>(&Qs[i][c]);
+        s = fmaf(qv.x, k[c], s); s = fmaf(qv.y, k[c + 1], s); s = fmaf(qv.z, k[c + 2], s); s = fmaf(qv.w, k[c + 3], s);
+      }
       const float p = expf(s * scale - Ls[i]);
       if (WHICH == 1) {
 #pragma unroll
-        for (int c = 0; c < 64; ++c) acc[c] = fmaf(p, Gs[i][c], acc[c]);
+        for (int c = 0; c < 64; c += 4) {
+          const float4 gv = *reinterpret_cast<const float4*>(&Gs[i][c]);
+          acc[c] = fmaf(p, gv.x, acc[c]); acc[c + 1] = fmaf(p, gv.y, acc[c + 1]);
+          acc[c + 2] = fmaf(p, gv.z, acc[c + 2]); acc[c + 3] = fmaf(p, gv.w, acc[c + 3]);
+        }
       } else {
         float dp = 0.0f;
 #pragma unroll
-        for (int c = 0; c < 64; ++c) dp = fmaf(Gs[i][c], v[c], dp);
+        for (int c = 0; c < 64; c += 4) {
+          const float4 gv = *reinterpret_cast<const float4*>(&Gs[i][c]);
+          dp = fmaf(gv.x, v[c], dp); dp = fmaf(gv.y, v[c + 1], dp); dp = fmaf(gv.z, v[c + 2], dp); dp = fmaf(gv.w, v[c + 3], dp);
+        }
         const float ds = p * (dp - Ds[i]) * scale;
 #pragma unroll
-        for (int c = 0; c < 64; ++c) acc[c] = fmaf(ds, Qs[i][c], acc[c]);
+        for (int c = 0; c < 64; c += 4) {
+          const float4 qv = *reinterpret_cast<const float4*>(&Qs[i][c]);
+          acc[c] = fmaf(ds, qv.x, acc[c]); acc[c + 1] = fmaf(ds, qv.y, acc[c + 1]);
+          acc[c + 2] = fmaf(ds, qv.z, acc[c + 2]); acc[c + 3] = fmaf(ds, qv.w, acc[c + 3]);
+        }
       }
     }
   }
@@ -490,6 +513,72 @@ void attention_backward(cudaStream_t st, const float* qkv, const float* o, const
   attn_dkv_kernel<0><<<grid, AB_T, 0, st>>>(qkv, d_o, lse, D, rows, heads, kv_len, scale, dqkv);
   F5B_POST_LAUNCH();
   attn_dkv_kernel<1><<<grid, AB_T, 0, st>>>(qkv, d_o, lse, D, rows, heads, kv_len, scale, dqkv);
+  F5B_POST_LAUNCH();
+}
+
+}  // namespace f5b
+
+namespace f5b {
+
+// ---------------------------------------------------------------------------------------------
+// 16-bit operand preparation for the tensor-core tier of the backward GEMMs (tc_gemm computes A[M,K] W[N,K]^T):
+//   cast16           : fp32 [R, C] -> 16-bit [R, ldd], columns >= C zero (ldd = C rounded up to 8: TMA stride rule)
+//   transpose_cast16 : fp32 [R, C] -> 16-bit [C, ldd], ldd >= R, columns >= R zero (32 x 32 tiles through shared memory)
+// fp16 = 1: IEEE half (forward operands), 0: bf16 (gradient operands need the exponent range)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint16_t to16(float v, int fp16) {
+  if (fp16) {
+    __half h = __float2half_rn(v);
+    return *reinterpret_cast<uint16_t*>(&h);
+  }
+  bf16 h = __float2bfloat16_rn(v);
+  return *reinterpret_cast<uint16_t*>(&h);
+}
+__global__ void __launch_bounds__(256)
+cast16_kernel(const float* __restrict__ src, long long lds, long long R, int C, uint16_t* __restrict__ dst, long long ldd,
+              int fp16) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= R * ldd) return;
+  const long long r = i / ldd;
+  const int c = (int)(i - r * ldd);
+  dst[i] = c < C ? to16(src[r * lds + c], fp16) : (uint16_t)0;
+}
+void cast16(cudaStream_t st, const float* src, long long lds, long long R, int C, void* dst, long long ldd, int fp16) {
+  cast16_kernel<<<cdiv(R * ldd, 256), 256, 0, st>>>(src, lds, R, C, reinterpret_cast<uint16_t*>(dst), ldd, fp16);
+  F5B_POST_LAUNCH();
+}
+__global__ void __launch_bounds__(256)
+transpose_cast16_kernel(const float* __restrict__ src, long long lds, long long R, int C, uint16_t* __restrict__ dst,
+                        long long ldd, int fp16) {
+  __shared__ float tile[32][33];
+  const long long r0 = (long long)blockIdx.x * 32;
+  const int c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  for (int k = ty; k < 32; k += 8) {
+    const long long r = r0 + k;
+    const int c = c0 + tx;
+    tile[k][tx] = (r < R && c < C) ? src[r * lds + c] : 0.0f;
+  }
+  __syncthreads();
+  for (int k = ty; k < 32; k += 8) {
+    const int c = c0 + k;
+    const long long r = r0 + tx;
+    if (c < C && r < ldd) dst[(long long)c * ldd + r] = to16(tile[tx][k], fp16);  // rows >= R were read as zero
+  }
+}
+__global__ void __launch_bounds__(256)
+widen_bf16_kernel(const bf16* __restrict__ src, long long n, float* __restrict__ dst) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i < n) dst[i] = __bfloat162float(src[i]);
+}
+void widen_bf16(cudaStream_t st, const void* src, long long n, float* dst) {
+  widen_bf16_kernel<<<cdiv(n, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(src), n, dst);
+  F5B_POST_LAUNCH();
+}
+void transpose_cast16(cudaStream_t st, const float* src, long long lds, long long R, int C, void* dst, long long ldd,
+                      int fp16) {
+  transpose_cast16_kernel<<<dim3(cdiv(ldd, 32), cdiv(C, 32)), 256, 0, st>>>(src, lds, R, C, reinterpret_cast<uint16_t*>(dst),
+                                                                           ldd, fp16);
   F5B_POST_LAUNCH();
 }
 

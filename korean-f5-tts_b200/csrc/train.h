@@ -51,7 +51,16 @@ void grn_bwd(cudaStream_t st, const float* dg, const float* a, int batches, int 
              const float* gamma, float* stats, const float* mu, float* part, float* da, float* dgamma, float* dbeta);
 void embed_bwd(cudaStream_t st, const float* dte, const long long* text, int B, int nt, int drop_text, int rows, int td,
                const int* row_len, int mask_padding, int masked_fill_applies, int table_rows, float* dtable);
+void conv_w_flipT_bf16(cudaStream_t st, const float* w, void* out, int C, int groups, int taps);
 void vec_add_const(cudaStream_t st, const float* v, float k, int n, float* out);
 void col_slice(cudaStream_t st, const float* x, long long ldx, int off, int w, long long rows, float* y, long long ldy,
                int yoff);
+}  // namespace f5b
+
+namespace f5b {
+// 16-bit operands for the tensor-core tier of the backward GEMMs (train.cu)
+void cast16(cudaStream_t st, const float* src, long long lds, long long R, int C, void* dst, long long ldd, int fp16);
+void transpose_cast16(cudaStream_t st, const float* src, long long lds, long long R, int C, void* dst, long long ldd,
+                      int fp16);
+void widen_bf16(cudaStream_t st, const void* src, long long n, float* dst);
 }  // namespace f5b

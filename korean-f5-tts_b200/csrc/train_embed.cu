@@ -367,6 +367,21 @@ void embed_bwd(cudaStream_t st, const float* dte, const long long* text, int B, 
   F5B_POST_LAUNCH();
 }
 
+// Weights of the data-gradient of a grouped Conv1d as a forward convolution (tensor-core tier, implicit-GEMM layout of
+// tc_gemm's conv mode: [c_out][tap * cg + c_in]):  dx = conv(dz, w'),  w'[ci][tap' * cg + co_l] = w[g cg + co_l][ci_l][taps-1-tap']
+__global__ void conv_w_flipT_bf16_kernel(const float* __restrict__ w, bf16* __restrict__ out, int C, int cg, int taps) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= (long long)C * cg * taps) return;
+  const int col = (int)(i % (cg * taps)), ci = (int)(i / (cg * taps));
+  const int tp = col / cg, co_l = col - tp * cg, g = ci / cg, ci_l = ci - g * cg;
+  out[i] = __float2bfloat16_rn(w[((long long)(g * cg + co_l) * cg + ci_l) * taps + (taps - 1 - tp)]);
+}
+void conv_w_flipT_bf16(cudaStream_t st, const float* w, void* out, int C, int groups, int taps) {
+  const int cg = C / groups;
+  conv_w_flipT_bf16_kernel<<<cdiv2((long long)C * cg * taps, 256), 256, 0, st>>>(w, reinterpret_cast<bf16*>(out), C, cg, taps);
+  F5B_POST_LAUNCH();
+}
+
 // out[c] = v[c] + k
 __global__ void vec_add_const_kernel(const float* __restrict__ v, float k, int n, float* __restrict__ out) {
   const int i = blockIdx.x * 256 + threadIdx.x;

@@ -51,3 +51,37 @@ def test_two_rank_request_sharding_gloo():
     loads = [sum(sharding.request_cost(lengths[i]) for i in s) for s in sharding.shard_requests(lengths, 2)]
     assert max(loads) / min(loads) < 1.05  # LPT balance
     assert mine0 == sharding.shard_requests(lengths, 2)[0]
+
+
+def _ddp_worker(rank, world, port, out_q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from f5b200.train import TrainStep
+
+        ts = TrainStep.__new__(TrainStep)  # the exchange itself: no device, no model needed
+        ts.group = None
+        ts.flat_grad = torch.arange(10, dtype=torch.float32) * (rank + 1)  # rank r holds (r + 1) * [0..9]
+        avg = ts.reduce_gradients()
+        dist.barrier()
+        out_q.put((rank, avg, ts.flat_grad.clone()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gradient_exchange_gloo():
+    """The training step's only collective (reference trainer.py:59-70: DDP averages gradients): one all-reduce (sum) of
+    the flat gradient buffer; the 1 / world factor is returned and folded into the optimiser's gradient read."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_ddp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(2)], key=lambda x: x[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, avg, g in res:
+        assert avg == 0.5 and torch.equal(g, torch.arange(10, dtype=torch.float32) * 3)  # sum on every rank
+        assert torch.equal(g * avg, torch.arange(10, dtype=torch.float32) * 1.5)          # the mean of the two ranks

@@ -65,7 +65,7 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.rows, self.proc, self.index = [], None, index
+        self.rows, self.proc, self.index, self.t_begin = [], None, index, None
 
     def start(self):
         try:
@@ -78,12 +78,18 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def begin(self):
+        """Samples from here on count (nvidia-smi is started earlier: on an 8-GPU box its start-up alone is longer
+        than a short timed region)."""
+        self.t_begin = time.perf_counter()
 
     def stop(self) -> dict:
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
+        self.rows = [r for t, r in self.rows if self.t_begin is None or t >= self.t_begin]
         sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -612,13 +618,14 @@ def run_ours(args, rank: int, world: int, local_rank: int):
 
     with torch.cuda.stream(stream):
         # -------- value: device-resident inputs, CUDA events on the launching stream --------
+        clk = ClockSampler(local_rank)
+        clk.start()  # running before the warm-up so that samples exist from the first timed step on
         for i in range(args.warmup):
             step_device(i)
         for i in range(extra_warm):  # several processes start together: let clocks / allocator / page-ins settle
             step_device(i % max(args.warmup, 1))
         barrier()
-        clk = ClockSampler(local_rank)
-        clk.start()
+        clk.begin()
         l0 = L.lib().f5b_launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
@@ -627,7 +634,6 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         e1.record(stream)
         barrier()
         launches = L.lib().f5b_launch_count() - l0
-        clocks = clk.stop()
         ms_total = reduce_max(e0.elapsed_time(e1))
         assert torch.isfinite(wav).all(), "non-finite waveform"
         check = check_against_oracle(last["mel"], last["seed"])
@@ -641,6 +647,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         torch.cuda.synchronize(dev)
         e2e_s = reduce_max(time.perf_counter() - t0)
         barrier()
+        clocks = clk.stop()  # sampled every 100 ms over the two timed regions (device-resident and end-to-end steps)
+        clocks["window"] = "device-timed + e2e-timed steps"
         h2d = sum(t.numel() * t.element_size() for t in pin_in[0])
         d2h = w.numel() * w.element_size()
         roof = roofline_gemm(stream, pk) if rank == 0 else None

@@ -246,3 +246,46 @@ def test_text_id_out_of_range_raises_index_error():
             cfm._ode(*host)
     again, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), duration=40, steps=2, cfg_strength=2.0, seed=1)
     assert torch.equal(good, again)
+
+
+def test_two_threads_share_one_plan():
+    """The reference samples from a thread pool (infer/utils_infer.py:725-727).  Two host threads calling `sample` on
+    the SAME model (one plan, one workspace, one graph cache) serialise on the plan's mutex: each gets the bits it gets
+    alone, also when the two requests have different lengths (the second one's workspace / graph must not disturb the
+    first one's in-flight call)."""
+    import threading
+
+    cfg = O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2)
+    sd = O.synth_backbone_weights(cfg, seed=2)
+    cfm = build_cfm(cfg, sd, "fp32")
+    g = torch.Generator().manual_seed(11)
+    jobs = {}
+    for n in (72, 100):
+        cond, text = O.synth_inputs(n, 20, 7, seed=n)
+        jobs[n] = (cond.cuda(), text.cuda(), torch.randn(1, n, 100, generator=g))
+
+    def run(n):
+        cond, text, y0 = jobs[n]
+        out = cfm.sample(cond=cond, text=text, y0=y0, duration=n, steps=4, cfg_strength=2.0, sway_sampling_coef=-1.0)[0]
+        torch.cuda.synchronize()
+        return out.cpu()
+
+    alone = {n: run(n) for n in jobs}
+    got, errs = {}, []
+
+    def worker(n, reps=6):
+        try:
+            with torch.cuda.stream(torch.cuda.Stream()):
+                got[n] = [run(n) for _ in range(reps)]
+        except Exception as e:  # noqa: BLE001 - reported below
+            errs.append(e)
+
+    ths = [threading.Thread(target=worker, args=(n,)) for n in jobs]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs
+    for n in jobs:
+        for out in got[n]:
+            assert torch.equal(out, alone[n])

@@ -129,6 +129,15 @@ int f5b_op_adamw(float* param, const float* grad, float* exp_avg, float* exp_avg
                  float beta1, float beta2, float eps, float weight_decay, int32_t step, float grad_scale,
                  float ema_decay, int32_t device, void* stream);
 
+/* Allocation-free variant of f5b_op_sumsq.  NO counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it).  The 1024 double partials that f5b_op_sumsq takes as `scratch` live in a file-scope `static __device__` array
+ * of the library (8 KB on every GPU that loads it, held until exit), so the call allocates nothing on host or device;
+ * x and out are device pointers supplied by the caller.  Limit: n <= 2^31 elements (F5B_ERR_INVALID with a message
+ * beyond it).  All calls share the one array: calls that overlap on the GPU (different streams or threads) race; calls
+ * ordered on one stream are safe.  Nothing needs clearing between calls (every partial is overwritten).  Asynchronous. */
+int f5b_op_sumsq_static(const float* x, int64_t n, double* out, int32_t device, void* stream);
+
 /* Replaces MelSpec.forward (model/modules.py:78-104,133-146): wav [B, nw] -> mel [B, 100, nw/256 + 1]. */
 int f5b_mel(const float* wav, int32_t B, int32_t nw, float* mel, int32_t device, int32_t mem, void* stream);
 

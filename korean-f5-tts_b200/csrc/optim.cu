@@ -3,6 +3,9 @@
 // torch.optim.AdamW semantics (decoupled weight decay, bias correction).
 #include "plan.h"
 
+#include <mutex>
+#include <string>
+
 namespace f5b {
 
 DeviceCtx open_device(int device, int mode);
@@ -46,11 +49,65 @@ __global__ void sumsq_final_kernel(const double* __restrict__ part, double* __re
   *out = acc;
 }
 
+// ---- allocation-free variant (f5b_op_sumsq_static) -------------------------------------------------------------
+// The 1024 block partials live in this file-scope device array instead of a caller-supplied scratch buffer, so the
+// entry point needs no device allocation from anyone (callers under CUDA-graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc).  Every GPU that loads the library holds the 8 KB until exit.  In HOST code the name
+// `g_sumsq_scratch` is only a stand-in for the symbol, not a device address: the host resolves it once per device with
+// cudaGetSymbolAddress (device current) and passes that pointer to the kernels.  All calls share the array (it keeps
+// the last call's partials): calls that overlap on the GPU -- two streams, two host threads -- race on it.
+static constexpr long long SQ_STATIC_MAX_N = 1LL << 31;  // 2 Gi elements = 8 GiB of fp32
+static __device__ __align__(256) double g_sumsq_scratch[SQ_BLOCKS];
+static constexpr int SQ_MAX_DEVICES = 64;
+static double* g_sumsq_scratch_ptr[SQ_MAX_DEVICES] = {};
+static std::mutex g_sumsq_mu;
+
+// Device address of the scratch array on `device` (resolved once per device, with that device current).
+static double* sumsq_scratch_on(int device) {
+  F5B_REQUIRE(device >= 0 && device < SQ_MAX_DEVICES, "device index beyond the scratch table");
+  std::lock_guard<std::mutex> lock(g_sumsq_mu);
+  if (g_sumsq_scratch_ptr[device] == nullptr) {
+    int n = 0;
+    F5B_CHECK_CUDA(cudaGetDeviceCount(&n));
+    F5B_REQUIRE(device < n, "device index out of range");
+    F5B_CHECK_CUDA(cudaSetDevice(device));
+    double* ptr = nullptr;
+    F5B_CHECK_CUDA(cudaGetSymbolAddress((void**)&ptr, g_sumsq_scratch));
+    F5B_REQUIRE(ptr != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    g_sumsq_scratch_ptr[device] = ptr;
+  }
+  return g_sumsq_scratch_ptr[device];
+}
+
 }  // namespace f5b
 
 using namespace f5b;
 
 extern "C" {
+
+// f5b_op_sumsq without a scratch argument and without any allocation (see g_sumsq_scratch above).  x, out: device
+// pointers; n <= 2^31.  Nothing in the scratch has to start at zero: every one of the 1024 blocks overwrites its
+// partial on every call.  Asynchronous on `stream`; calls that overlap on the GPU race on the shared scratch.
+int f5b_op_sumsq_static(const float* x, int64_t n, double* out, int32_t device, void* stream) {
+  try {
+    F5B_REQUIRE(x && out && n > 0, "bad argument");
+    if (n > SQ_STATIC_MAX_N) {
+      set_error("f5b_op_sumsq_static: n = " + std::to_string((long long)n) + " exceeds the maximum of " +
+                std::to_string(SQ_STATIC_MAX_N) + " elements of the allocation-free variant (use f5b_op_sumsq)");
+      return F5B_ERR_INVALID;
+    }
+    double* scratch = sumsq_scratch_on(device);
+    F5B_CHECK_CUDA(cudaSetDevice(device));
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    sumsq_partial_kernel<<<SQ_BLOCKS, 256, 0, st>>>(x, n, scratch);
+    F5B_POST_LAUNCH();
+    sumsq_final_kernel<<<1, 1, 0, st>>>(scratch, out);
+    F5B_POST_LAUNCH();
+  } catch (const f5b::Err& e) {
+    return e.code;
+  }
+  return F5B_OK;
+}
 
 // sum_i x[i]^2 in double precision -> *out (device pointer, 1 double); scratch: device, >= 1024 doubles.  Asynchronous.
 int f5b_op_sumsq(const float* x, int64_t n, double* scratch, double* out, int32_t device, void* stream) {

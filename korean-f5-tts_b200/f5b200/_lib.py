@@ -70,6 +70,7 @@ _SIGNATURES = {
     "f5b_cfm_loss_tail_grads": (C.c_int, [C.c_void_p] * 7 + [C.c_int32] * 5 + [C.c_void_p, C.POINTER(Grad), C.c_int32,
                                                                         C.c_int32, C.c_void_p]),
     "f5b_op_sumsq": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
+    "f5b_op_sumsq_static": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p]),
     "f5b_op_adamw": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
                                C.c_float, C.c_float, C.c_float, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_void_p]),
     "f5b_op_time": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float), C.c_int32,

@@ -173,6 +173,11 @@ int f5b_op_istft(const float* z, int64_t ldz, const int32_t* lens, int32_t B, in
                  void* stream);
 int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int32_t batches, int32_t rows,
                      int32_t heads, float* out, int32_t device, void* stream);
+/* Backward of the same attention (what autograd runs behind modules.py:499-508 under trainer.py:384): given qkv and
+ * d_out [batches*rows, heads*64], dqkv [batches*rows, 3*heads*64] receives dq | dk | dv.  mode fp32: CUDA-core kernels;
+ * mode bf16: tcgen05 kernels (forward recompute with log-sum-exp, then tc_attn_dq / tc_attn_dkv). */
+int f5b_op_attention_bwd(int32_t mode, const float* qkv, const float* d_out, const int32_t* kv_len, int32_t batches,
+                         int32_t rows, int32_t heads, float* dqkv, int32_t device, void* stream);
 /* Times `iters` back-to-back launches of one kernel with CUDA events on `stream`; returns average ms in *ms.
  *   which: 0 = bf16 tcgen05 GEMM [M,K]x[N,K] (64/128/256: forced tile width; 4: gate*y+residual epilogue), 1 = bf16 tcgen05 attention (M = rows, N = heads, K = batches),
  *          2 = LN+modulate (M rows, N = dim). */

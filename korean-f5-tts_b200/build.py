@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "f5b200", "libf5b200.so")
 OBJ = os.path.join(HERE, "build")
-SOURCES = ["runtime.cu", "rowwise.cu", "simt.cu", "tc_gemm.cu", "tc_attn.cu", "backbone.cu", "stft.cu", "vocos.cu", "resample.cu", "train.cu", "train_embed.cu", "optim.cu"]
+SOURCES = ["runtime.cu", "rowwise.cu", "simt.cu", "tc_gemm.cu", "tc_attn.cu", "tc_attn_bwd.cu", "backbone.cu", "stft.cu", "vocos.cu", "resample.cu", "train.cu", "train_embed.cu", "optim.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC"]
 if os.environ.get("F5B_KTRACE") == "1":  # debug build: in-situ kernel timeline (csrc/common.cuh, tools/ktrace.py)

@@ -5,6 +5,7 @@
 #include <cstring>
 
 #include "plan.h"
+#include "train.h"
 
 namespace f5b {
 
@@ -238,6 +239,7 @@ DeviceCtx open_device(int device, int mode) {
   c.sm_count = p.multiProcessorCount;
   if (!g_kernels_ready) {
     tc_init_kernels();
+    tc_attn_bwd_init_kernels();
     tc_gemm_init_kernels();
     simt_init_kernels();
     g_kernels_ready = true;
@@ -323,6 +325,35 @@ int f5b_op_attention(int32_t mode, const float* qkv, const int32_t* kv_len, int3
   F5B_API_END
 }
 
+
+int f5b_op_attention_bwd(int32_t mode, const float* qkv, const float* d_out, const int32_t* kv_len, int32_t batches,
+                         int32_t rows, int32_t heads, float* dqkv, int32_t device, void* stream) {
+  F5B_API_BEGIN
+  open_device(device, mode);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const long long M = (long long)batches * rows;
+  const int inner = heads * 64;
+  Arena arena;
+  float* o = arena.alloc_n<float>((size_t)M * inner);
+  float* lse = arena.alloc_n<float>((size_t)M * heads);
+  float* D = arena.alloc_n<float>((size_t)M * heads);
+  if (mode == F5B_MODE_BF16) {
+    bf16* q16 = arena.alloc_n<bf16>((size_t)M * 3 * inner);
+    bf16* o16 = arena.alloc_n<bf16>((size_t)M * inner);
+    bf16* do16 = arena.alloc_n<bf16>((size_t)M * inner);
+    f32_to_bf16(st, qkv, q16, M * 3 * inner);
+    tc_attention(st, q16, o16, batches, rows, heads, kv_len, 0.125f, 0, lse);
+    widen_kernel<<<(unsigned)((M * inner + 255) / 256), 256, 0, st>>>(o16, o, M * inner);
+    F5B_POST_LAUNCH();
+    attn_bwd_prep(st, o, d_out, batches, rows, heads, do16, D);
+    tc_attention_backward(st, q16, do16, lse, D, batches, rows, heads, kv_len, 0.125f, dqkv);
+  } else {
+    simt_attention(st, qkv, o, batches, rows, heads, kv_len, 0.125f);
+    attention_backward(st, qkv, o, d_out, batches, rows, heads, kv_len, 0.125f, lse, D, dqkv);
+  }
+  F5B_CHECK_CUDA(cudaStreamSynchronize(st));
+  F5B_API_END
+}
 
 /* Debug: run the tcgen05 attention once on constant data with the in-kernel timeline enabled; out[3][64][8] receives
  * clock64 stamps of CTA (0,0,0): who 0/1 = softmax tile 0/1 {wait S, S ready, max done, P handed over}, who 2 = MMA

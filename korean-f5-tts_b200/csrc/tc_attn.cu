@@ -27,10 +27,11 @@
 //           S / P*V MMAs).
 //   EARLY : P lives in its own TMEM columns instead of over S, so S_t(j+1) is issued as soon as S_t(j) has been read
 //           into registers and its MMA time leaves the tile's dependency chain.
-//   POLY  : POLY of every 4 element pairs take exp2 on the FMA pipe instead of the MUFU (Cody-Waite split by a
+//   POLY  : POLY of every 8 elements take exp2 on the FMA pipe instead of the MUFU (Cody-Waite split by a
 //           magic-number add, degree-3 minimax polynomial on [-0.5, 0.5], max relative error 7.6e-5 -- 50x below the
-//           bf16 rounding of P -- exponent inserted with one LEA), in packed f32x2 instructions.
-//   The scale-and-subtract and the row sum use fma.rn.f32x2 / add.rn.f32x2 throughout (half the issue slots).
+//           bf16 rounding of P -- exponent inserted with one LEA).
+//   All softmax arithmetic is scalar: packed f32x2 forms issue at half the per-element rate (tools/ubench/pipes.cu).
+//   Measured (profiles/r2_attn_variants.log): SEQ wins 5-7 %, EARLY and POLY lose; default variant = 100.
 #include "common.cuh"
 #include "sm100_ptx.cuh"
 #include "tc_gemm.h"
@@ -83,7 +84,7 @@ __device__ __forceinline__ float exp2_poly(float x) {
 template <int SEQ, int EARLY, int POLY>
 __global__ void __launch_bounds__(320, 1)
 tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, int rows, int heads,
-               const int* __restrict__ kv_len, float scale_log2, int out_f16) {
+               const int* __restrict__ kv_len, float scale_log2, int out_f16, float* __restrict__ lse2_out) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sQ = smem;                                  // 2 tiles
@@ -333,6 +334,8 @@ tc_attn_kernel(const __grid_constant__ CUtensorMap tm, bf16* __restrict__ out, i
     tc_fence_after();                                               //  below store 0 * inf = NaN like softmax over an
     const int r = q0 + t * AT_BQ + row;                             //  empty set in the reference)
     const float inv = 1.0f / l;
+    // training: the row's log-sum-exp in the log2 domain, P = exp2(s * scale_log2 - lse2) (read by tc_attn_bwd.cu)
+    if (lse2_out != nullptr && r < rows) lse2_out[((long long)b * heads + h) * rows + r] = fmaf(m_ref, scale_log2, log2f(l));
     bf16* op = out + ((long long)b * rows + r) * inner + h * AT_D;
 #pragma unroll
     for (int c = 0; c < AT_D; c += 32) {
@@ -374,7 +377,7 @@ KT_DEFINE_SETTER(ktrace_set_tc_attn)
 // Variant code = SEQ * 100 + EARLY * 10 + POLY (F5B_ATTN_VARIANT overrides the default; read at every launch so one
 // process can time them against each other).  0 is the round-1 kernel (nanosleep stagger, scalar arithmetic aside).
 static constexpr int AT_DEFAULT_VARIANT = 100;  // measured best on B200 at the C2 / C3 / C4 shapes (profiles/r2_attn_variants.log)
-typedef void (*AttnKernel)(const CUtensorMap, bf16*, int, int, const int*, float, int);
+typedef void (*AttnKernel)(const CUtensorMap, bf16*, int, int, const int*, float, int, float*);
 static AttnKernel attn_kernel_for(int v) {
   switch (v) {
     case 0: return tc_attn_kernel<0, 0, 0>;
@@ -391,7 +394,7 @@ static AttnKernel attn_kernel_for(int v) {
 static const int kAttnVariants[] = {0, 10, 11, 100, 110, 111, 112, 113};
 
 void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int rows, int heads, const int* kv_len,
-                  float scale, int out_f16) {
+                  float scale, int out_f16, float* lse2_out) {
   const int inner = heads * AT_D;
   CUtensorMap tm;
   uint64_t dims[3] = {(uint64_t)3 * inner, (uint64_t)rows, (uint64_t)batches};
@@ -402,7 +405,8 @@ void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int 
   const char* env = std::getenv("F5B_ATTN_VARIANT");
   AttnKernel k = attn_kernel_for(env ? std::atoi(env) : AT_DEFAULT_VARIANT);
   F5B_REQUIRE(k != nullptr, "unknown F5B_ATTN_VARIANT");
-  launch_pdl_id(2, k, grid, dim3(320), AT_SMEM, st, tm, out, rows, heads, kv_len, scale * 1.4426950408889634f, out_f16);
+  launch_pdl_id(2, k, grid, dim3(320), AT_SMEM, st, tm, out, rows, heads, kv_len, scale * 1.4426950408889634f, out_f16,
+                lse2_out);
   F5B_POST_LAUNCH();
 }
 

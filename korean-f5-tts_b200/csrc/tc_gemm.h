@@ -52,7 +52,16 @@ void simt_group_conv(cudaStream_t st, const float* x, int batches, int rows, int
 // bf16 tensor-core attention (tcgen05) and fp32 CUDA-core attention.  qkv [batches*rows, 3*heads*64]; out
 // [batches*rows, heads*64].  kv_len[b] (or rows when null) keys take part.
 void tc_attention(cudaStream_t st, const bf16* qkv, bf16* out, int batches, int rows, int heads, const int* kv_len,
-                  float scale, int out_f16 = 0 /* output written as IEEE fp16 (operand of the next GEMM) */);
+                  float scale, int out_f16 = 0 /* output written as IEEE fp16 (operand of the next GEMM) */,
+                  float* lse2_out = nullptr /* [batches, heads, rows] log2-domain log-sum-exp (training) */);
+// Backward of the same attention on the tensor cores (tc_attn_bwd.cu).  qkv bf16 as above, d_o bf16 [batches*rows,
+// heads*64], lse2 from the forward, D[b,h,r] = sum_d dO O; dqkv fp32 [batches*rows, 3*heads*64] receives dq | dk | dv.
+void tc_attention_backward(cudaStream_t st, const bf16* qkv, const bf16* d_o, const float* lse2, const float* D,
+                           int batches, int rows, int heads, const int* kv_len, float scale, float* dqkv);
+// d_o16 = bf16(d_o), D[b,h,r] = sum_d d_o[r, h*64+d] * o[r, h*64+d]   (one pass over both fp32 inputs)
+void attn_bwd_prep(cudaStream_t st, const float* o, const float* d_o, int batches, int rows, int heads, bf16* d_o16,
+                   float* D);
+void tc_attn_bwd_init_kernels();
 void simt_attention(cudaStream_t st, const float* qkv, float* out, int batches, int rows, int heads, const int* kv_len,
                     float scale);
 

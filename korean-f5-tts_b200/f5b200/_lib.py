@@ -66,6 +66,8 @@ _SIGNATURES = {
                               C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "f5b_op_attention": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                    C.c_int32, C.c_void_p]),
+    "f5b_op_attention_bwd": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                       C.c_void_p, C.c_int32, C.c_void_p]),
     "f5b_cfm_loss": (C.c_int, [C.c_void_p] * 7 + [C.c_int32] * 5 + [C.c_void_p] * 3 + [C.c_int32, C.c_void_p]),
     "f5b_cfm_loss_tail_grads": (C.c_int, [C.c_void_p] * 7 + [C.c_int32] * 5 + [C.c_void_p, C.POINTER(Grad), C.c_int32,
                                                                         C.c_int32, C.c_void_p]),

@@ -134,3 +134,57 @@ def test_op_time_runs():
     ms = C.c_float()
     L.check(L.lib().f5b_op_time(0, 512, 512, 512, 3, C.byref(ms), 0, 0))
     assert ms.value > 0
+
+
+def _attention_bwd(mode, qkv, d_out, kv_len, batches, rows, heads):
+    L = _lib()
+    dev = torch.device("cuda", 0)
+    q_d, g_d = qkv.to(dev).contiguous(), d_out.to(dev).contiguous()
+    l_d = kv_len.to(dev, torch.int32).contiguous() if kv_len is not None else None
+    out = torch.full((batches * rows, 3 * heads * 64), float("nan"), device=dev)
+    L.check(L.lib().f5b_op_attention_bwd(mode, q_d.data_ptr(), g_d.data_ptr(), L.ptr(l_d), batches, rows, heads,
+                                         out.data_ptr(), 0, 0))
+    return out.cpu()
+
+
+def _attention_bwd_ref(qkv, d_out, kv_len, batches, rows, heads):
+    """torch.autograd through the same softmax(q k^T / 8) v (what trainer.py:384 runs behind modules.py:499-508)."""
+    x = qkv.double().clone().requires_grad_(True)
+    y = x.view(batches, rows, 3, heads, 64)
+    q, k, v = (y[:, :, i].transpose(1, 2) for i in range(3))
+    s = q @ k.transpose(-1, -2) * 0.125
+    if kv_len is not None:
+        keep = torch.arange(rows)[None, :] < kv_len[:, None]
+        s = s.masked_fill(~keep[:, None, None, :], float("-inf"))
+    o = (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(batches * rows, heads * 64)
+    o.backward(d_out.double())
+    return x.grad.float()
+
+
+@pytest.mark.parametrize("mode,tol", [(0, 1e-4), (1, 2e-2)])
+@pytest.mark.parametrize("batches,rows,heads,lens", [(1, 100, 2, None), (2, 333, 3, [333, 201]), (2, 940, 4, [940, 700]),
+                                                      (1, 1024, 2, [128])])
+def test_attention_backward(mode, tol, batches, rows, heads, lens):
+    """dq | dk | dv of the attention core: fp32 CUDA-core kernels (mode 0) and the tcgen05 kernels (mode 1: bf16
+    operands, P and dS rounded to bf16, fp32 accumulation) against autograd in float64.  Rows past an utterance's length
+    carry no upstream gradient (the caller masks them, modules.py:540-542) and their keys take no part."""
+    g = torch.Generator().manual_seed(rows + heads)
+    qkv = torch.randn(batches * rows, 3 * heads * 64, generator=g)
+    d_out = torch.randn(batches * rows, heads * 64, generator=g)
+    kv = torch.tensor(lens) if lens else None
+    if kv is not None:
+        dead = (torch.arange(rows)[None, :] >= kv[:, None]).reshape(-1)
+        d_out[dead] = 0.0
+    if mode == 1:  # the kernel's operands are bf16: compare on what it was given
+        qkv = qkv.bfloat16().float()
+    got = _attention_bwd(mode, qkv, d_out, kv, batches, rows, heads)
+    ref = _attention_bwd_ref(qkv, d_out, kv, batches, rows, heads)
+    assert torch.isfinite(got).all()
+    err = (got - ref).abs().max()
+    assert err <= tol * max(1.0, float(ref.abs().max())), f"max err {err} (ref max {ref.abs().max()})"
+    # relative Frobenius error per third: a wrong scale or a swapped block would pass a loose max-abs bound
+    inner = heads * 64
+    for i, name in enumerate(("dq", "dk", "dv")):
+        a, b = got[:, i * inner:(i + 1) * inner], ref[:, i * inner:(i + 1) * inner]
+        rel = float((a - b).norm() / b.norm())
+        assert rel <= (1e-5 if mode == 0 else 1e-2), f"{name}: relative error {rel}"

@@ -494,8 +494,7 @@ C5_BATCH, C5_FRAMES = 40, 960  # 38 400 frames per GPU per step (configs/F5TTS_v
 
 def run_c5(dev, stream, rank: int, world: int, pk: dict, steps: int = 2, warmup: int = 1) -> dict:
     """F5TTS_v1_Base training step, WEAK scaling (38 400 frames per GPU, trainer.py:59-70 DDP): 16-bit tensor-core forward,
-    backward of every parameter (GEMMs and grouped convolutions on tcgen05 with bf16 operands, attention backward still
-    on the CUDA cores), ONE NCCL all-reduce of the 1.34 GB fp32 gradient over NVLink, global-norm clip, fused AdamW.
+    backward of every parameter (GEMMs, grouped convolutions and attention on tcgen05 with bf16 operands), ONE NCCL all-reduce of the 1.34 GB fp32 gradient over NVLink, global-norm clip, fused AdamW.
     Timed per step with CUDA events, max over ranks; the all-reduce is timed on its own as well."""
     import torch.distributed as dist
 
@@ -517,7 +516,7 @@ def run_c5(dev, stream, rank: int, world: int, pk: dict, steps: int = 2, warmup:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
             loss = ts.step(x1, text, lens=lens)
-            cfm.transformer.plan()  # the next step's packed 16-bit weights belong to this step's cost
+            cfm.transformer.plan()  # (no-op: TrainStep.step re-packs the 16-bit weights into the plan itself)
             e1.record(stream)
             torch.cuda.synchronize(dev)
             if i >= warmup:
@@ -543,8 +542,9 @@ def run_c5(dev, stream, rank: int, world: int, pk: dict, steps: int = 2, warmup:
             "allreduce_ms": round(ar_ms, 3), "allreduce_bytes": nparam * 4,
             "allreduce_busbw_GBps": round(2 * (world - 1) / world * nparam * 4 / (ar_ms / 1e3) / 1e9, 1) if world > 1 else None,
             "loss_first_last": [round(losses[0], 4), round(losses[-1], 4)],
-            "note": "the attention backward runs on the CUDA cores (fp32) and is about half of the step; fp32 master "
-                    "weights / gradients / Adam moments; the all-reduce is not overlapped with the backward yet"}
+            "note": "every GEMM, the grouped convolutions and the attention (forward recompute and backward) run on "
+                    "tcgen05; fp32 master weights / gradients / Adam moments; the all-reduce is not overlapped with "
+                    "the backward yet"}
 
 
 # ---- our arm -------------------------------------------------------------------------------------------------------

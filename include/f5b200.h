@@ -68,6 +68,11 @@ int f5b_device_check(int device);
 int f5b_plan_create(const f5b_arch* arch, const f5b_tensor* weights, int32_t n_weights, int32_t mode, int32_t device,
                     f5b_plan** out);
 void f5b_plan_destroy(f5b_plan* plan);
+/* After the optimiser has changed the weights (model/trainer.py:388 optimizer.step(); the reference's modules simply
+ * read the updated nn.Parameters on the next forward): copy + re-pack the same state dict (same names and sizes as at
+ * creation) into the plan's existing device buffers.  No allocation; workspace and graphs stay valid.  Synchronous:
+ * waits for `stream` (the stream the update ran on) first and returns when the new weights are in place. */
+int f5b_plan_refresh(f5b_plan* plan, const f5b_tensor* weights, int32_t n_weights, void* stream);
 
 /* Replaces the ODE part of CFM.sample (model/cfm.py:160-219): text-embedding cache, EPSS/sway grid consumption,
  * CFG-doubled backbone evaluations, Euler updates.  Inputs are what cfm.py:104-216 builds on the host:

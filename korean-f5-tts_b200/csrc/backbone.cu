@@ -95,6 +95,7 @@ struct f5b_plan {
   DeviceCtx ctx;
   f5b_arch a;
   Arena warena;
+  Arena train_ws;  // workspace of the training step (backbone_train.inc), kept between steps
   std::unique_ptr<WeightStore> ws;
   std::unique_ptr<Arena> wk;  // workspace arena
   Bufs bf;
@@ -134,6 +135,8 @@ struct f5b_plan {
 
   f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, int device);
   ~f5b_plan();
+  void build_weights(const f5b_tensor* w, int n, cudaStream_t st);  // copies + packs every weight into `warena`
+  void refresh_weights(const f5b_tensor* w, int n);                 // the same again over the same buffers
   void ensure_ws(int B, int N, int nt, int steps, bool want_traj);
   template <typename T> void text_embed(cudaStream_t st, int B, int N, int nt, int batches, int text_uncond_from,
                                         int cond_uncond_from, const int* lens_text);
@@ -158,25 +161,11 @@ f5b_plan::~f5b_plan() {
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 
-f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, int device) : a(arch) {
-  F5B_REQUIRE(mode == F5B_MODE_FP32 || mode == F5B_MODE_BF16, "unknown precision mode");
-  F5B_REQUIRE(a.backbone == F5B_BACKBONE_DIT || a.backbone == F5B_BACKBONE_UNETT, "unknown backbone");
-  F5B_REQUIRE(a.dim_head == 64, "only dim_head 64 is built (all shipped configs)");
-  F5B_REQUIRE(a.dim % 16 == 0 && a.mel_dim % 4 == 0 && a.text_dim % 4 == 0, "unsupported widths");
-  ctx = open_device(device, mode);
-  use_graph = std::getenv("F5B_NO_GRAPH") == nullptr;
-  F5B_CHECK_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
-  is_dit = a.backbone == F5B_BACKBONE_DIT;
-  inner = a.heads * 64;
-  R_extra = is_dit ? 0 : 1;
-  td = a.text_dim;
-  kin = 2 * a.mel_dim + td;
-  kin_ld = (kin + 7) / 8 * 8;
-  pe_heads = a.pe_attn_head > 0 ? a.pe_attn_head : a.heads;
+void f5b_plan::build_weights(const f5b_tensor* w, int n, cudaStream_t st) {
+  const int mode = ctx.mode;
   const int d = a.dim, ffd = a.dim * a.ff_mult;
-  if (mode == F5B_MODE_BF16) F5B_REQUIRE((d / 16) % 64 == 0, "bf16 mode needs dim/16 channels per conv group to be a multiple of 64");
-
-  cudaStream_t st = 0;
+  tblocks.clear();
+  layers.clear();
   ws.reset(new WeightStore(&warena, w, n, st));
   auto W = [&](const std::string& nm, long long numel) { return ws->get(nm, numel); };
 
@@ -274,7 +263,49 @@ f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, i
   // the velocity goes straight into the ODE state: proj_out is contracted with ~16-bit operands in bf16 mode
   proj_out = make_wmat_split3(ctx, &warena, st, W("proj_out.weight", (long long)a.mel_dim * d), a.mel_dim, d);
   b_out = W("proj_out.bias", a.mel_dim);
+}
 
+// After an optimiser step (f5b_plan_refresh): the SAME sequence of copies / packing kernels over the SAME device
+// buffers (Arena replay), so the weights change under the plan without a single cudaMalloc / cudaFree, the workspace
+// and the captured graphs (which hold pointers into these buffers) stay valid.
+void f5b_plan::refresh_weights(const f5b_tensor* w, int n) {
+  F5B_CHECK_CUDA(cudaSetDevice(ctx.device));
+  std::lock_guard<std::mutex> lock(mu);
+  F5B_CHECK_CUDA(cudaStreamSynchronize(own_stream));  // nothing of an earlier call may still read the old values
+  const size_t before = warena.blocks();
+  warena.begin_replay();
+  try {
+    build_weights(w, n, 0);
+  } catch (...) {
+    warena.end_replay();
+    throw;
+  }
+  warena.end_replay();
+  F5B_REQUIRE(warena.blocks() == before, "the refreshed state dict does not have the shape of the plan's");
+  cache_valid = false;
+  F5B_CHECK_CUDA(cudaStreamSynchronize(0));
+}
+
+f5b_plan::f5b_plan(const f5b_arch& arch, const f5b_tensor* w, int n, int mode, int device) : a(arch) {
+  F5B_REQUIRE(mode == F5B_MODE_FP32 || mode == F5B_MODE_BF16, "unknown precision mode");
+  F5B_REQUIRE(a.backbone == F5B_BACKBONE_DIT || a.backbone == F5B_BACKBONE_UNETT, "unknown backbone");
+  F5B_REQUIRE(a.dim_head == 64, "only dim_head 64 is built (all shipped configs)");
+  F5B_REQUIRE(a.dim % 16 == 0 && a.mel_dim % 4 == 0 && a.text_dim % 4 == 0, "unsupported widths");
+  ctx = open_device(device, mode);
+  use_graph = std::getenv("F5B_NO_GRAPH") == nullptr;
+  F5B_CHECK_CUDA(cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking));
+  is_dit = a.backbone == F5B_BACKBONE_DIT;
+  inner = a.heads * 64;
+  R_extra = is_dit ? 0 : 1;
+  td = a.text_dim;
+  kin = 2 * a.mel_dim + td;
+  kin_ld = (kin + 7) / 8 * 8;
+  pe_heads = a.pe_attn_head > 0 ? a.pe_attn_head : a.heads;
+  const int d = a.dim, ffd = a.dim * a.ff_mult;
+  if (mode == F5B_MODE_BF16) F5B_REQUIRE((d / 16) % 64 == 0, "bf16 mode needs dim/16 channels per conv group to be a multiple of 64");
+
+  cudaStream_t st = 0;
+  build_weights(w, n, st);
   // frequency tables, computed the way the reference does (fp32 pow / exp of fp32 arguments)
   std::vector<float> ft(td / 2), fr(32), tf(128);
   for (int j = 0; j < td / 2; ++j) ft[j] = 1.0f / powf(10000.0f, (float)(2 * j) / (float)td);          // modules.py:202-213

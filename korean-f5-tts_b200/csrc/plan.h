@@ -19,6 +19,10 @@ struct DeviceCtx {
 };
 
 // Owns cudaMalloc'd blocks; everything is released together.
+// Replay: code that allocates a deterministic sequence of buffers (the plan's weight packing, the training step's
+// workspace) can be run again over the SAME blocks -- begin_replay() rewinds, alloc() then hands out the existing
+// blocks in order (a block whose size no longer matches is replaced, further requests are appended), so a repeated
+// call costs no cudaMalloc / cudaFree (each of which synchronises the device).
 class Arena {
  public:
   ~Arena() { release(); }
@@ -27,10 +31,15 @@ class Arena {
   T* alloc_n(size_t n) { return reinterpret_cast<T*>(alloc(n * sizeof(T))); }
   void release();
   size_t total() const { return total_; }
+  void begin_replay() { replay_ = 0; }
+  void end_replay() { replay_ = (size_t)-1; }
+  size_t blocks() const { return blocks_.size(); }
 
  private:
   std::vector<void*> blocks_;
+  std::vector<size_t> sizes_;
   size_t total_ = 0;
+  size_t replay_ = (size_t)-1;  // index of the next block to hand out again; -1: not replaying
 };
 
 // A weight matrix usable by either contraction path: fp32 [N, K] always; bf16 [N, ldw] in bf16 mode.

@@ -34,15 +34,33 @@ void* Arena::alloc(size_t bytes) {
   void* p = nullptr;
   size_t b = (bytes + 255) & ~size_t(255);
   if (b == 0) b = 256;
+  if (replay_ != (size_t)-1 && replay_ < blocks_.size()) {
+    const size_t i = replay_++;
+    if (sizes_[i] == b) return blocks_[i];
+    F5B_CHECK_CUDA(cudaFree(blocks_[i]));  // the sequence changed shape here: replace this block
+    blocks_[i] = nullptr;
+    total_ -= sizes_[i];
+    sizes_[i] = 0;
+    F5B_CHECK_CUDA(cudaMalloc(&p, b));
+    blocks_[i] = p;
+    sizes_[i] = b;
+    total_ += b;
+    return p;
+  }
   F5B_CHECK_CUDA(cudaMalloc(&p, b));
   blocks_.push_back(p);
+  sizes_.push_back(b);
   total_ += b;
+  if (replay_ != (size_t)-1) replay_ = blocks_.size();
   return p;
 }
 void Arena::release() {
-  for (void* p : blocks_) cudaFree(p);
+  for (void* p : blocks_)
+    if (p) cudaFree(p);
   blocks_.clear();
+  sizes_.clear();
   total_ = 0;
+  replay_ = (size_t)-1;
 }
 
 WeightStore::WeightStore(Arena* arena, const f5b_tensor* w, int n, cudaStream_t st) {

@@ -18,12 +18,18 @@ static inline unsigned cdiv(long long a, long long b) { return (unsigned)((a + b
 __global__ void __launch_bounds__(256)
 sgemm_strided_kernel(const float* __restrict__ A, long long sa0, long long sa1, const float* __restrict__ B,
                      long long sb0, long long sb1, float* __restrict__ C, long long ldc, int M, int N, int K,
-                     int accumulate) {
+                     int accumulate, int k_slice) {
   __shared__ float As[16][64 + 1], Bs[16][64 + 1];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
   float acc[4][4] = {};
-  for (int k0 = 0; k0 < K; k0 += 16) {
+  int kbeg = 0;
+  if (k_slice > 0) {  // split-K: slice blockIdx.z of the contraction into its own [M, N] partial (C = scratch, ldc = N)
+    kbeg = blockIdx.z * k_slice;
+    K = min(K, kbeg + k_slice);
+    C += (long long)blockIdx.z * M * N;
+  }
+  for (int k0 = kbeg; k0 < K; k0 += 16) {
     for (int e = tid; e < 64 * 16; e += 256) {
       // contiguous index first along whichever dimension is unit-stride in memory
       int i, k;
@@ -60,10 +66,45 @@ sgemm_strided_kernel(const float* __restrict__ A, long long sa0, long long sa1, 
     }
 }
 
+// Skinny product with a long contraction (ds += dmod [B, 6d] W_ada [6d, d]: 40 x 1024 x 6144): 16 CTAs walking 384
+// k-blocks each took 0.55 ms.  K is cut into `splits` slices (blockIdx.z), every slice writes its partial into the
+// scratch, a second kernel adds the slices in order (deterministic) into C.
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ part, int splits, long long mn, int N, float* __restrict__ C, long long ldc,
+                     int accumulate) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= mn) return;
+  float acc = 0.0f;
+  for (int s = 0; s < splits; ++s) acc += part[(long long)s * mn + i];
+  float* c = C + (i / N) * ldc + (i % N);
+  *c = accumulate ? *c + acc : acc;
+}
+static thread_local float* g_splitk_scratch = nullptr;
+static thread_local size_t g_splitk_scratch_floats = 0;
+void sgemm_set_scratch(float* p, size_t floats) {
+  g_splitk_scratch = p;
+  g_splitk_scratch_floats = floats;
+}
 void sgemm_strided(cudaStream_t st, const float* A, long long sa0, long long sa1, const float* B, long long sb0,
                    long long sb1, float* C, long long ldc, int M, int N, int K, bool accumulate) {
+  if (M <= 64 && K >= 1024 && g_splitk_scratch != nullptr) {
+    int splits = K / 96;  // slices of >= 96 (a multiple of the 16-deep k-block)
+    if (splits > 64) splits = 64;
+    while (splits > 1 && (size_t)splits * M * N > g_splitk_scratch_floats) --splits;
+    if (splits > 1) {
+      const int k_slice = ((K + splits - 1) / splits + 15) / 16 * 16;
+      splits = (K + k_slice - 1) / k_slice;
+      sgemm_strided_kernel<<<dim3(cdiv(N, 64), cdiv(M, 64), splits), 256, 0, st>>>(A, sa0, sa1, B, sb0, sb1,
+                                                                                  g_splitk_scratch, N, M, N, K, 0, k_slice);
+      F5B_POST_LAUNCH();
+      splitk_reduce_kernel<<<cdiv((long long)M * N, 256), 256, 0, st>>>(g_splitk_scratch, splits, (long long)M * N, N, C,
+                                                                       ldc, accumulate ? 1 : 0);
+      F5B_POST_LAUNCH();
+      return;
+    }
+  }
   sgemm_strided_kernel<<<dim3(cdiv(N, 64), cdiv(M, 64)), 256, 0, st>>>(A, sa0, sa1, B, sb0, sb1, C, ldc, M, N, K,
-                                                                          accumulate ? 1 : 0);
+                                                                          accumulate ? 1 : 0, 0);
   F5B_POST_LAUNCH();
 }
 
@@ -107,6 +148,10 @@ static thread_local size_t g_colsum_scratch_floats = 0;
 void colsum_set_scratch(float* p, size_t floats) {
   g_colsum_scratch = p;
   g_colsum_scratch_floats = floats;
+}
+float* colsum_scratch(size_t* floats) {
+  *floats = g_colsum_scratch_floats;
+  return g_colsum_scratch;
 }
 void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
                   long long out_bstride) {
@@ -207,12 +252,42 @@ gelu_tanh_bwd_kernel(const float* __restrict__ u, const float* __restrict__ dh, 
   const float t = tanhf(k * (x + c * x * x * x));
   du[i] = dh[i] * (0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * k * (1.0f + 3.0f * c * x * x));
 }
+__device__ __forceinline__ float gelu_tanh_grad(float x, float dh) {
+  const float k = 0.7978845608028654f, c = 0.044715f;
+  const float t = tanhf(k * (x + c * x * x * x));
+  return dh * (0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * k * (1.0f + 3.0f * c * x * x));
+}
+// four elements per thread (16-byte accesses): the scalar forms above ran at a third of the HBM rate
+__global__ void __launch_bounds__(256)
+gelu_tanh_fwd4_kernel(const float4* __restrict__ u, float4* __restrict__ h, long long n4) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n4) return;
+  const float4 x = u[i];
+  h[i] = make_float4(act_apply(ACT_GELU_TANH, x.x), act_apply(ACT_GELU_TANH, x.y), act_apply(ACT_GELU_TANH, x.z),
+                     act_apply(ACT_GELU_TANH, x.w));
+}
+__global__ void __launch_bounds__(256)
+gelu_tanh_bwd4_kernel(const float4* __restrict__ u, const float4* __restrict__ dh, float4* __restrict__ du, long long n4) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n4) return;
+  const float4 x = u[i], g = dh[i];
+  du[i] = make_float4(gelu_tanh_grad(x.x, g.x), gelu_tanh_grad(x.y, g.y), gelu_tanh_grad(x.z, g.z), gelu_tanh_grad(x.w, g.w));
+}
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 void gelu_tanh_fwd(cudaStream_t st, const float* u, float* h, long long n) {
-  gelu_tanh_fwd_kernel<<<cdiv(n, 256), 256, 0, st>>>(u, h, n);
+  if (n % 4 == 0 && al16(u) && al16(h))
+    gelu_tanh_fwd4_kernel<<<cdiv(n / 4, 256), 256, 0, st>>>(reinterpret_cast<const float4*>(u), reinterpret_cast<float4*>(h), n / 4);
+  else
+    gelu_tanh_fwd_kernel<<<cdiv(n, 256), 256, 0, st>>>(u, h, n);
   F5B_POST_LAUNCH();
 }
 void gelu_tanh_bwd(cudaStream_t st, const float* u, const float* dh, float* du, long long n) {
-  gelu_tanh_bwd_kernel<<<cdiv(n, 256), 256, 0, st>>>(u, dh, du, n);
+  if (n % 4 == 0 && al16(u) && al16(dh) && al16(du))
+    gelu_tanh_bwd4_kernel<<<cdiv(n / 4, 256), 256, 0, st>>>(reinterpret_cast<const float4*>(u),
+                                                          reinterpret_cast<const float4*>(dh),
+                                                          reinterpret_cast<float4*>(du), n / 4);
+  else
+    gelu_tanh_bwd_kernel<<<cdiv(n, 256), 256, 0, st>>>(u, dh, du, n);
   F5B_POST_LAUNCH();
 }
 
@@ -242,8 +317,35 @@ rowscale_kernel(const float* __restrict__ x, const float* __restrict__ v, long l
   const bool dead = row_len != nullptr && pos >= row_len[b];
   out[i] = dead ? 0.0f : (v ? v[b * vec_bstride + c] : 1.0f) * x[i];
 }
+__global__ void __launch_bounds__(256)
+rowscale4_kernel(const float4* __restrict__ x, const float* __restrict__ v, long long vec_bstride, int rows_per_batch,
+                 const int* __restrict__ row_len, int cols4, long long total4, float4* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total4) return;
+  const long long m = i / cols4;
+  const int c = (int)(i - m * cols4) * 4;
+  const long long b = m / rows_per_batch;
+  const int pos = (int)(m - b * rows_per_batch);
+  if (row_len != nullptr && pos >= row_len[b]) {
+    out[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    return;
+  }
+  float4 a = x[i];
+  if (v) {
+    const float4 s = *reinterpret_cast<const float4*>(v + b * vec_bstride + c);
+    a.x *= s.x; a.y *= s.y; a.z *= s.z; a.w *= s.w;
+  }
+  out[i] = a;
+}
 void rowscale(cudaStream_t st, const float* x, const float* v, long long vec_bstride, int rows_per_batch,
               const int* row_len, long long M, int cols, float* out) {
+  if (cols % 4 == 0 && vec_bstride % 4 == 0 && al16(x) && al16(out) && (v == nullptr || al16(v))) {
+    rowscale4_kernel<<<cdiv(M * (cols / 4), 256), 256, 0, st>>>(reinterpret_cast<const float4*>(x), v, vec_bstride,
+                                                               rows_per_batch, row_len, cols / 4, M * (cols / 4),
+                                                               reinterpret_cast<float4*>(out));
+    F5B_POST_LAUNCH();
+    return;
+  }
   rowscale_kernel<<<cdiv(M * cols, 256), 256, 0, st>>>(x, v, vec_bstride, rows_per_batch, row_len, cols, M * cols, out);
   F5B_POST_LAUNCH();
 }
@@ -253,8 +355,20 @@ axpy_kernel(float* __restrict__ y, const float* __restrict__ x, float a, long lo
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i < n) y[i] += a * x[i];
 }
+__global__ void __launch_bounds__(256)
+axpy4_kernel(float4* __restrict__ y, const float4* __restrict__ x, float a, long long n4) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n4) return;
+  float4 r = y[i];
+  const float4 v = x[i];
+  r.x += a * v.x; r.y += a * v.y; r.z += a * v.z; r.w += a * v.w;
+  y[i] = r;
+}
 void axpy(cudaStream_t st, float* y, const float* x, float a, long long n) {
-  axpy_kernel<<<cdiv(n, 256), 256, 0, st>>>(y, x, a, n);
+  if (n % 4 == 0 && al16(y) && al16(x))
+    axpy4_kernel<<<cdiv(n / 4, 256), 256, 0, st>>>(reinterpret_cast<float4*>(y), reinterpret_cast<const float4*>(x), a, n / 4);
+  else
+    axpy_kernel<<<cdiv(n, 256), 256, 0, st>>>(y, x, a, n);
   F5B_POST_LAUNCH();
 }
 
@@ -543,7 +657,29 @@ cast16_kernel(const float* __restrict__ src, long long lds, long long R, int C, 
   const int c = (int)(i - r * ldd);
   dst[i] = c < C ? to16(src[r * lds + c], fp16) : (uint16_t)0;
 }
+// C, lds, ldd multiples of 4 and 16-byte aligned rows: one float4 in, four 16-bit values out per thread
+__global__ void __launch_bounds__(256)
+cast16x4_kernel(const float* __restrict__ src, long long lds, long long R, int C, uint16_t* __restrict__ dst, long long ldd,
+                int fp16) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long q = ldd / 4;
+  if (i >= R * q) return;
+  const long long r = i / q;
+  const int c = (int)(i - r * q) * 4;
+  uint2 o = make_uint2(0u, 0u);
+  if (c < C) {
+    const float4 v = *reinterpret_cast<const float4*>(src + r * lds + c);
+    o.x = (uint32_t)to16(v.x, fp16) | ((uint32_t)to16(v.y, fp16) << 16);
+    o.y = (uint32_t)to16(v.z, fp16) | ((uint32_t)to16(v.w, fp16) << 16);
+  }
+  *reinterpret_cast<uint2*>(dst + r * ldd + c) = o;
+}
 void cast16(cudaStream_t st, const float* src, long long lds, long long R, int C, void* dst, long long ldd, int fp16) {
+  if (C % 4 == 0 && lds % 4 == 0 && ldd % 4 == 0 && al16(src) && (reinterpret_cast<uintptr_t>(dst) & 7) == 0) {
+    cast16x4_kernel<<<cdiv(R * (ldd / 4), 256), 256, 0, st>>>(src, lds, R, C, reinterpret_cast<uint16_t*>(dst), ldd, fp16);
+    F5B_POST_LAUNCH();
+    return;
+  }
   cast16_kernel<<<cdiv(R * ldd, 256), 256, 0, st>>>(src, lds, R, C, reinterpret_cast<uint16_t*>(dst), ldd, fp16);
   F5B_POST_LAUNCH();
 }
@@ -566,17 +702,58 @@ transpose_cast16_kernel(const float* __restrict__ src, long long lds, long long 
     if (c < C && r < ldd) dst[(long long)c * ldd + r] = to16(tile[tx][k], fp16);  // rows >= R were read as zero
   }
 }
+// 64 source rows x 32 source columns per CTA: a warp reads 128 B of a source row and writes 128 B (64 packed 16-bit
+// values) of a destination row -- the 32 x 32 tile above wrote 64-byte pieces
+__global__ void __launch_bounds__(256)
+transpose_cast16w_kernel(const float* __restrict__ src, long long lds, long long R, int C, uint16_t* __restrict__ dst,
+                         long long ldd, int fp16) {
+  __shared__ float tile[32][65];  // [source column][source row]
+  const long long r0 = (long long)blockIdx.x * 64;
+  const int c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int k = ty; k < 64; k += 8) {
+    const long long r = r0 + k;
+    const int c = c0 + tx;
+    tile[tx][k] = (r < R && c < C) ? src[r * lds + c] : 0.0f;
+  }
+  __syncthreads();
+  for (int k = ty; k < 32; k += 8) {
+    const int c = c0 + k;
+    const long long r = r0 + 2 * tx;  // ldd is even (asserted by the launcher): r + 1 < ldd whenever r < ldd
+    if (c < C && r < ldd)
+      *reinterpret_cast<uint32_t*>(dst + (long long)c * ldd + r) =
+          (uint32_t)to16(tile[k][2 * tx], fp16) | ((uint32_t)to16(tile[k][2 * tx + 1], fp16) << 16);
+  }
+}
+__global__ void __launch_bounds__(256)
+widen_bf16x4_kernel(const uint2* __restrict__ src, long long n4, float4* __restrict__ dst) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= n4) return;
+  const uint2 v = src[i];
+  dst[i] = make_float4(__uint_as_float(v.x << 16), __uint_as_float(v.x & 0xffff0000u), __uint_as_float(v.y << 16),
+                       __uint_as_float(v.y & 0xffff0000u));
+}
 __global__ void __launch_bounds__(256)
 widen_bf16_kernel(const bf16* __restrict__ src, long long n, float* __restrict__ dst) {
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i < n) dst[i] = __bfloat162float(src[i]);
 }
 void widen_bf16(cudaStream_t st, const void* src, long long n, float* dst) {
-  widen_bf16_kernel<<<cdiv(n, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(src), n, dst);
+  if (n % 4 == 0 && al16(dst) && (reinterpret_cast<uintptr_t>(src) & 7) == 0)
+    widen_bf16x4_kernel<<<cdiv(n / 4, 256), 256, 0, st>>>(reinterpret_cast<const uint2*>(src), n / 4,
+                                                        reinterpret_cast<float4*>(dst));
+  else
+    widen_bf16_kernel<<<cdiv(n, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(src), n, dst);
   F5B_POST_LAUNCH();
 }
 void transpose_cast16(cudaStream_t st, const float* src, long long lds, long long R, int C, void* dst, long long ldd,
                       int fp16) {
+  if (ldd % 2 == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
+    transpose_cast16w_kernel<<<dim3(cdiv(ldd, 64), cdiv(C, 32)), 256, 0, st>>>(src, lds, R, C,
+                                                                              reinterpret_cast<uint16_t*>(dst), ldd, fp16);
+    F5B_POST_LAUNCH();
+    return;
+  }
   transpose_cast16_kernel<<<dim3(cdiv(ldd, 32), cdiv(C, 32)), 256, 0, st>>>(src, lds, R, C, reinterpret_cast<uint16_t*>(dst),
                                                                            ldd, fp16);
   F5B_POST_LAUNCH();

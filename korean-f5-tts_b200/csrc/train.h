@@ -7,6 +7,9 @@ namespace f5b {
 // C[i,j] (+)= sum_k A[i*sa0 + k*sa1] * B[k*sb0 + j*sb1]
 void sgemm_strided(cudaStream_t st, const float* A, long long sa0, long long sa1, const float* B, long long sb0,
                    long long sb1, float* C, long long ldc, int M, int N, int K, bool accumulate);
+// scratch for the split-K form of skinny products (M <= 64, K >= 1024): >= 64 * M * N floats to use all 64 slices
+void sgemm_set_scratch(float* p, size_t floats);
+float* colsum_scratch(size_t* floats);  // the buffer handed to colsum_set_scratch (shared by the depthwise-conv wgrad)
 // out[b*out_bstride + j] = sum_{r in batch b} X[r,j] * (Y ? Y[r,j] : 1)
 void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
                   long long out_bstride);

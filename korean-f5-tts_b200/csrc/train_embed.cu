@@ -4,6 +4,8 @@
 // reduction has one owner thread or a fixed tree).  Activations are channels-last: [batch, rows, channels].
 #include "train.h"
 
+#include <algorithm>
+
 namespace f5b {
 
 static inline unsigned cdiv2(long long a, long long b) { return (unsigned)((a + b - 1) / b); }
@@ -188,8 +190,59 @@ gconv_wgrad64_kernel(const float* __restrict__ dz, const float* __restrict__ x, 
     for (int j = 0; j < 4; ++j)
       dw[((long long)(g * 64 + ty * 4 + i) * 64 + tx * 4 + j) * taps + tap] = acc[i][j];
 }
+// Depthwise (one channel per group; the ConvNeXt blocks' k = 7 convolution, modules.py:246): the rows are cut into
+// `chunks` slices, a thread owns one channel of one slice and keeps its `taps` sums in registers (coalesced over the
+// channels), the slices are added in order by a second kernel.  The generic kernel above walked all rows in ONE thread
+// per weight: 20 ms per call at 38 400 rows.
+template <int TAPS>
+__global__ void __launch_bounds__(256)
+dwconv_wgrad_part_kernel(const float* __restrict__ dz, const float* __restrict__ x, int rows, int C,
+                         const int* __restrict__ row_len, long long M, long long rows_per_chunk, float* __restrict__ part) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  const long long m0 = (long long)blockIdx.y * rows_per_chunk, m1 = min(M, m0 + rows_per_chunk);
+  constexpr int pad = TAPS / 2;
+  float acc[TAPS];
+#pragma unroll
+  for (int k = 0; k < TAPS; ++k) acc[k] = 0.0f;
+  for (long long m = m0; m < m1; ++m) {
+    const int b = (int)(m / rows), t = (int)(m - (long long)b * rows);
+    const int len = row_len ? row_len[b] : rows;
+    const float g = dz[m * C + c];
+#pragma unroll
+    for (int k = 0; k < TAPS; ++k) {
+      const int tt = t + k - pad;
+      if (tt >= 0 && tt < len) acc[k] = fmaf(g, x[((long long)b * rows + tt) * C + c], acc[k]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < TAPS; ++k) part[((long long)blockIdx.y * TAPS + k) * C + c] = acc[k];
+}
+__global__ void __launch_bounds__(256)
+dwconv_wgrad_sum_kernel(const float* __restrict__ part, int chunks, int C, int taps, float* __restrict__ dw) {
+  const int i = blockIdx.x * 256 + threadIdx.x;  // = c * taps + tap (PyTorch layout [C, 1, taps])
+  if (i >= C * taps) return;
+  const int c = i / taps, k = i - c * taps;
+  float acc = 0.0f;
+  for (int s = 0; s < chunks; ++s) acc += part[((long long)s * taps + k) * C + c];
+  dw[i] = acc;
+}
+
 void gconv_wgrad(cudaStream_t st, const float* dz, const float* x, int batches, int rows, int C, int groups, int taps,
                  const int* row_len, float* dw) {
+  size_t scratch_floats = 0;
+  float* scratch = colsum_scratch(&scratch_floats);
+  if (groups == C && taps == 7 && scratch != nullptr && scratch_floats >= (size_t)8 * taps * C) {
+    const long long M = (long long)batches * rows;
+    int chunks = (int)std::min<size_t>(128, scratch_floats / ((size_t)taps * C));
+    const long long rpc = (M + chunks - 1) / chunks;
+    chunks = (int)((M + rpc - 1) / rpc);
+    dwconv_wgrad_part_kernel<7><<<dim3(cdiv2(C, 256), chunks), 256, 0, st>>>(dz, x, rows, C, row_len, M, rpc, scratch);
+    F5B_POST_LAUNCH();
+    dwconv_wgrad_sum_kernel<<<cdiv2((long long)C * taps, 256), 256, 0, st>>>(scratch, chunks, C, taps, dw);
+    F5B_POST_LAUNCH();
+    return;
+  }
   if (C / groups == 64) {
     gconv_wgrad64_kernel<<<dim3(groups, taps), 256, 0, st>>>(dz, x, batches, rows, C, taps, row_len, dw);
     F5B_POST_LAUNCH();

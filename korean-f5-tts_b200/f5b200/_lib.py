@@ -66,6 +66,7 @@ _SIGNATURES = {
                               C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "f5b_op_attention": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                    C.c_int32, C.c_void_p]),
+    "f5b_plan_refresh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "f5b_op_attention_bwd": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                        C.c_void_p, C.c_int32, C.c_void_p]),
     "f5b_cfm_loss": (C.c_int, [C.c_void_p] * 7 + [C.c_int32] * 5 + [C.c_void_p] * 3 + [C.c_int32, C.c_void_p]),

@@ -180,6 +180,18 @@ class _PlanBackbone(nn.Module):
         self._plan_sig = sig
         return handle
 
+    def refresh_plan(self):
+        """After parameters were updated in place behind torch's back (TrainStep's fused AdamW writes the flat buffer
+        the parameters are views of): re-pack the weights into the existing plan (no allocation, graphs stay valid)."""
+        if getattr(self, "_plan", None) is None:
+            return self.plan()
+        arr, keep = _lib.make_tensor_array(self.state_dict())
+        dev = next(self.parameters()).device
+        _lib.check(_lib.lib().f5b_plan_refresh(self._plan, arr, len(arr), _lib.current_stream_ptr(dev)))
+        del keep
+        self._plan_sig = self._signature()
+        return self._plan
+
     def synchronize(self):
         """Wait for the plan's last call and raise its deferred error.  Calls on CUDA tensors return once their work is
         enqueued (like any PyTorch CUDA operator); a token id outside the embedding table -- `nn.Embedding` would raise

@@ -96,7 +96,7 @@ class TrainStep:
                                   float(self.ema_decay or 0.0), _lib.device_index(self.device),
                                   _lib.current_stream_ptr(self.device)))
         ev[2].record()
-        self.tr.invalidate_plan()  # the plan packs its own 16-bit copies of the weights: rebuilt from the new values
+        self.tr.refresh_plan()  # the plan packs its own 16-bit copies of the weights: re-packed from the new values
         self.last = dict(grad_norm=float(norm), clip_coef=coef, events=ev)
         return loss
 

@@ -103,22 +103,28 @@ int f5b_plan_sync(f5b_plan* plan);
  * after the random draws (which stay host-side Python like the reference's): phi = (1 - t) x0 + t x1, cond = x1 outside
  * the random span, one backbone evaluation with the drop flags, MSE against x1 - x0 over the span frames.
  *   x1, x0 [B, N, mel]; time [B] HOST floats; lens [B] int32 or NULL; span [B, N] uint8 = rand_span_mask & lens mask.
- * Outputs: loss [1]; cond, pred [B, N, mel] (either may be NULL).  No gradients: the backward pass is not built. */
+ * Outputs: loss [1]; cond, pred [B, N, mel] (either may be NULL).  Gradients: f5b_cfm_loss_tail_grads below. */
 int f5b_cfm_loss(f5b_plan* plan, const float* x1, const float* x0, const int64_t* text, const float* time,
                  const int32_t* lens, const uint8_t* span, int32_t B, int32_t N, int32_t nt, int32_t drop_audio_cond,
                  int32_t drop_text, float* loss, float* cond, float* pred, int32_t mem, void* stream);
 
-/* Stage 1 of the training step's backward pass (model/trainer.py:384 `accelerator.backward(loss)` over
- * CFM.forward, cfm.py:231-302): the loss is differentiated through proj_out, the final AdaLN and the LAST DiTBlock
- * (dit.py:326-327, modules.py:683-697).  Same inputs as f5b_cfm_loss; each gradient slot names a parameter by its
- * state-dict name -- transformer_blocks.<depth-1>.{attn_norm.linear, attn.to_q|to_k|to_v|to_out.0, ff.ff.0.0, ff.ff.2}
- * .{weight,bias}, norm_out.linear.{weight,bias}, proj_out.{weight,bias} -- or "d_block_input" [B, N, dim] (gradient of
- * the residual stream entering the block) / "pred" [B, N, mel]; other names return F5B_ERR_MISSING.  fp32 CUDA-core
- * arithmetic in both precision modes.  Synchronous. */
+/* The backward pass of the training step (model/trainer.py:384 `accelerator.backward(loss)` over CFM.forward,
+ * cfm.py:231-302; DiT backbone): same inputs as f5b_cfm_loss; the loss is differentiated through proj_out, the final
+ * AdaLN, EVERY DiTBlock (dit.py:314-327, modules.py:683-697; each block recomputed from its saved input), the timestep
+ * MLP, InputEmbedding and TextEmbedding.  Each gradient slot names a parameter by its state-dict name (no
+ * "transformer." prefix), or "d_block_input" / "d_input_embed" [B, N, dim] (gradient of the residual stream entering the
+ * last block / block 0), or "pred" [B, N, mel]; other names return F5B_ERR_MISSING.  fp32 mode: CUDA-core arithmetic
+ * (parity tier); 16-bit mode: GEMMs, grouped convolutions and attention on tcgen05 with fp32 accumulation.  Gradients
+ * are written as soon as their layer is done (last block first).  `ready_event`, when not NULL, is a cudaEvent_t that
+ * the library records on its stream right after the slot has been written: slots of one all-reduce bucket share an
+ * event, and a communication stream that waits for it AFTER this call has returned sees the bucket complete (the
+ * gradient exchange of trainer.py:59-70 DDP then overlaps the rest of the backward pass).  Asynchronous for device
+ * buffers like every other entry. */
 typedef struct f5b_grad {
   const char* name;
   float* data; /* fp32, numel elements, same memory space as the inputs */
   int64_t numel;
+  void* ready_event; /* cudaEvent_t or NULL */
 } f5b_grad;
 int f5b_cfm_loss_tail_grads(f5b_plan* plan, const float* x1, const float* x0, const int64_t* text, const float* time,
                             const int32_t* lens, const uint8_t* span, int32_t B, int32_t N, int32_t nt,

@@ -34,7 +34,7 @@ class Tensor(C.Structure):
 
 
 class Grad(C.Structure):
-    _fields_ = [("name", C.c_char_p), ("data", C.c_void_p), ("numel", C.c_int64)]
+    _fields_ = [("name", C.c_char_p), ("data", C.c_void_p), ("numel", C.c_int64), ("ready_event", C.c_void_p)]
 
 
 _SIGNATURES = {

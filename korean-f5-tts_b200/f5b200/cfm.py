@@ -101,13 +101,15 @@ class CFM(nn.Module):
             _lib.mem_kind(x1), _lib.current_stream_ptr(dev)))
         return loss[0], cond, pred
 
-    def tail_gradients(self, inp, text, *, lens=None, draws: dict | None = None, names=None, buffers: dict | None = None):
+    def tail_gradients(self, inp, text, *, lens=None, draws: dict | None = None, names=None, buffers: dict | None = None,
+                       events: dict | None = None):
         """The backward pass (trainer.py:384 over CFM.forward): the loss and its gradients with respect to EVERY parameter
         of the DiT -- `{state-dict name: tensor}` with the reference's names (`transformer.` prefix included) -- plus
         `d_block_input` / `d_input_embed` (gradient of the residual stream entering the last block / block 0).  One
-        `f5b_cfm_loss_tail_grads` call; fp32 CUDA-core backward arithmetic in both precision modes, blocks recomputed
+        `f5b_cfm_loss_tail_grads` call; CUDA-core arithmetic in fp32 mode, tcgen05 kernels in 16-bit mode; blocks recomputed
         from their saved inputs (activation checkpointing); dropout is not modelled (eval-mode function).  `buffers`
-        ({name: preallocated fp32 tensor}) receives the gradients in place (the training step's flat gradient buffer)."""
+        ({name: preallocated fp32 tensor}) receives the gradients in place (the training step's flat gradient buffer);
+        `events` ({name: cudaEvent_t handle}) are recorded by the library as each gradient lands (TrainStep's buckets)."""
         import ctypes as C
 
         tr = self.transformer
@@ -126,7 +128,7 @@ class CFM(nn.Module):
             out[n if n in ("d_block_input", "d_input_embed", "pred") else "transformer." + n] = g
             bn = n.encode()
             keep.append(bn)
-            slots.append(_lib.Grad(bn, g.data_ptr(), g.numel()))
+            slots.append(_lib.Grad(bn, g.data_ptr(), g.numel(), events.get(n) if events else None))
         arr = (_lib.Grad * len(slots))(*slots)
         loss = torch.empty((1,), device=dev, dtype=torch.float32)
         _lib.check(_lib.lib().f5b_cfm_loss_tail_grads(

@@ -3,8 +3,11 @@ src/f5_tts/model/trainer.py:59-70 DDP through accelerate, :146 `AdamW(model.para
 :387 `clip_grad_norm_(max_grad_norm=1.0)`, :388-390 optimizer / scheduler step, :395 EMA update).
 
     loss, grads  <- f5b_cfm_loss_tail_grads   forward in the plan's precision mode + backward of every DiT parameter
-    all-reduce   <- ONE NCCL all-reduce of the flat gradient buffer over NVLink (sum; the 1 / world average is folded
-                    into the optimiser's gradient read) -- the only collective of the path
+    all-reduce   <- NCCL all-reduce (sum) of the flat gradient buffer over NVLink, in BUCKETS that follow the backward
+                    pass: [last block .. proj_out], then each earlier block, then the embeddings.  The library records a
+                    CUDA event per bucket as its last gradient lands; a communication stream waits for it, so the
+                    exchange of block l runs under the backward of blocks l-1 .. 0 (what DDP's bucketing does for the
+                    reference, trainer.py:59-70).  The 1 / world average is folded into the optimiser's gradient read
     clip         <- global L2 norm of the averaged gradient (f5b_op_sumsq), coefficient min(1, max_norm / (norm + 1e-6))
     update       <- f5b_op_adamw over the flat parameter / moment buffers (+ EMA copy)
 
@@ -19,6 +22,23 @@ from typing import Optional
 import torch
 
 from . import _lib
+
+
+def bucket_ranges(names, offsets, total):
+    """All-reduce buckets over the flat gradient buffer in the order the backward pass completes them: [last block ..
+    proj_out], block depth-2, ..., block 0, [embeddings].  The ranges are contiguous because named_parameters() lists
+    time_embed, text_embed, input_embed, transformer_blocks.0 .. depth-1, norm_out, proj_out in that order."""
+    first = {}
+    for nme, o in zip(names, offsets):
+        if nme.startswith("transformer_blocks."):
+            key = int(nme.split(".")[1])
+        else:  # the embeddings come before block 0; norm_out / proj_out follow the last block and complete with it
+            key = max(first) if any(k >= 0 for k in first) else -1
+        first.setdefault(key, o)
+    keys = sorted(first)
+    bounds = [first[k] for k in keys] + [total]
+    assert bounds == sorted(bounds), "parameters of one block are not contiguous in the flat buffer"
+    return [(bounds[i], bounds[i + 1]) for i in range(len(keys))][::-1]
 
 
 class TrainStep:
@@ -49,6 +69,15 @@ class TrainStep:
         self.ema = self.flat_param.clone() if ema_decay is not None else None
         self.grad_views = {n: self.flat_grad[o:o + s].view(p.shape) for (n, p), o, s in zip(params, self.offsets, sizes)}
         self._scratch = torch.empty(1025, device=dev, dtype=torch.float64)
+        self.buckets = bucket_ranges(self.names, self.offsets, n)  # last block first, embeddings last
+        self._bucket_of = {}
+        for nme, o in zip(self.names, self.offsets):
+            self._bucket_of[nme] = next(i for i, (a, b) in enumerate(self.buckets) if a <= o < b)
+        self._events = [torch.cuda.Event() for _ in self.buckets]
+        for e in self._events:
+            e.record()  # creates the CUDA event (torch makes it lazily) so that its handle can be given to the library
+        self._event_of = {nme: self._events[i].cuda_event for nme, i in self._bucket_of.items()}
+        self._comm = torch.cuda.Stream(device=dev)
         self.step_count = 0
         self.last = {}
         self.tr.invalidate_plan()
@@ -59,14 +88,26 @@ class TrainStep:
 
         return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1
 
-    def reduce_gradients(self):
-        """The data-parallel exchange: one all-reduce (sum) of the flat gradient buffer.  Returns the factor that turns
+    def reduce_gradients(self, overlapped: bool = True):
+        """The data-parallel exchange (sum) of the flat gradient buffer.  Called right after the backward pass has been
+        ENQUEUED (the library call is asynchronous): every bucket's all-reduce is issued on a communication stream behind
+        the event the library records when the bucket's last gradient has been written, so it runs while earlier blocks
+        are still being differentiated; the current stream then waits for all of them.  Returns the factor that turns
         the sum into the mean (folded into the optimiser's gradient read instead of a separate pass)."""
         import torch.distributed as dist
 
         w = self.world
-        if w > 1:
-            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+        if w > 1 and (not overlapped or not self.flat_grad.is_cuda):  # bucket after bucket on the current stream
+            for a, b in getattr(self, "buckets", None) or [(0, self.flat_grad.numel())]:
+                dist.all_reduce(self.flat_grad[a:b], op=dist.ReduceOp.SUM, group=self.group)
+        elif w > 1:
+            works = []
+            for ev, (a, b) in zip(self._events, self.buckets):
+                with torch.cuda.stream(self._comm):
+                    self._comm.wait_event(ev)
+                    works.append(dist.all_reduce(self.flat_grad[a:b], op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+            for wk in works:
+                wk.wait()  # the current stream waits for the communication (no host synchronisation)
         return 1.0 / w
 
     def grad_norm(self, scale: float = 1.0) -> torch.Tensor:
@@ -78,7 +119,8 @@ class TrainStep:
 
     def step(self, inp, text, *, lens=None, draws: dict | None = None, lr: Optional[float] = None):
         """forward + backward + all-reduce + clip + AdamW (+ EMA).  Returns the loss (0-dim device tensor)."""
-        loss, _ = self.cfm.tail_gradients(inp, text, lens=lens, draws=draws, names=self.names, buffers=self.grad_views)
+        loss, _ = self.cfm.tail_gradients(inp, text, lens=lens, draws=draws, names=self.names, buffers=self.grad_views,
+                                          events=self._event_of)
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
         ev[0].record()
         avg = self.reduce_gradients()

@@ -62,6 +62,7 @@ def _ddp_worker(rank, world, port, out_q):
         ts = TrainStep.__new__(TrainStep)  # the exchange itself: no device, no model needed
         ts.group = None
         ts.flat_grad = torch.arange(10, dtype=torch.float32) * (rank + 1)  # rank r holds (r + 1) * [0..9]
+        ts.buckets = [(6, 10), (2, 6), (0, 2)]  # exchanged bucket by bucket, in the backward pass's order
         avg = ts.reduce_gradients()
         dist.barrier()
         out_q.put((rank, avg, ts.flat_grad.clone()))
@@ -69,9 +70,20 @@ def _ddp_worker(rank, world, port, out_q):
         dist.destroy_process_group()
 
 
+def test_bucket_ranges_follow_the_backward_pass():
+    from f5b200.train import bucket_ranges
+
+    names = ["time_embed.w", "text_embed.w", "input_embed.w", "transformer_blocks.0.a", "transformer_blocks.0.b",
+             "transformer_blocks.1.a", "transformer_blocks.1.b", "transformer_blocks.2.a", "norm_out.w", "proj_out.w"]
+    offsets = [0, 3, 5, 9, 10, 14, 15, 20, 22, 25, 31]
+    # [block 2 + norm_out + proj_out], block 1, block 0, [embeddings]: every element exactly once
+    assert bucket_ranges(names, offsets, 31) == [(20, 31), (14, 20), (9, 14), (0, 9)]
+
+
 def test_two_rank_gradient_exchange_gloo():
-    """The training step's only collective (reference trainer.py:59-70: DDP averages gradients): one all-reduce (sum) of
-    the flat gradient buffer; the 1 / world factor is returned and folded into the optimiser's gradient read."""
+    """The training step's only collective (reference trainer.py:59-70: DDP averages gradients): all-reduce (sum) of the
+    flat gradient buffer, bucket by bucket; the 1 / world factor is returned and folded into the optimiser's gradient
+    read."""
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 31500 + os.getpid() % 2000

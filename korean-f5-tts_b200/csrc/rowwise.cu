@@ -756,10 +756,12 @@ void euler_xproj(cudaStream_t st, const float* y, float* y_next, const float* v,
                  float* hproj, int d) {
   F5B_REQUIRE(mel % 4 == 0 && d % 8 == 0 && ldw % 4 == 0, "euler_xproj needs mel % 4 == 0, dim % 8 == 0");
   const size_t smem = (size_t)(mel * XP_BN + XP_BM * (mel + 4)) * sizeof(float);
-  static size_t configured = 0;
-  if (smem > configured) {
+  static size_t configured[64] = {};  // per device: the limit is an attribute of the function ON a device
+  int dev = 0;
+  F5B_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || smem > configured[dev]) {
     F5B_CHECK_CUDA(cudaFuncSetAttribute(euler_xproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+    if (dev >= 0 && dev < 64) configured[dev] = smem;
   }
   const long long M1 = (long long)B * rows;
   dim3 grid(hproj ? (d + XP_BN - 1) / XP_BN : 1, (unsigned)((M1 + XP_BM - 1) / XP_BM));

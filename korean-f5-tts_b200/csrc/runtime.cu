@@ -3,6 +3,8 @@
 #include <cstdlib>
 #include <cmath>
 #include <cstring>
+#include <mutex>
+#include <string>
 
 #include "plan.h"
 #include "train.h"
@@ -224,7 +226,21 @@ void copy_out(void* dst, const void* src, size_t bytes, int mem, cudaStream_t st
   F5B_CHECK_CUDA(cudaMemcpyAsync(dst, src, bytes, mem == F5B_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
 }
 
-static void device_check_throw(int device) {
+// Device properties are queried ONCE per device (cudaGetDeviceProperties costs milliseconds; every f5b_op_* entry and
+// every optimiser step used to pay it twice) and the kernel attributes are set once per device as well.
+struct DeviceInfo {
+  bool checked = false, kernels_ready = false;
+  int major = 0, minor = 0, sm_count = 0;
+  std::string name;
+};
+static std::mutex g_dev_mu;
+static DeviceInfo g_dev[64];
+
+static DeviceInfo& device_check_throw(int device) {
+  if (device >= 0 && device < 64 && g_dev[device].checked && g_dev[device].major == 10) {  // fast path (written once)
+    F5B_CHECK_CUDA(cudaSetDevice(device));
+    return g_dev[device];
+  }
   int n = 0;
   cudaError_t e = cudaGetDeviceCount(&n);
   if (e != cudaSuccess || n == 0) {
@@ -232,35 +248,45 @@ static void device_check_throw(int device) {
     set_error(std::string("no CUDA device: libf5b200 has no CPU fallback (") + cudaGetErrorString(e) + ")");
     throw Err{F5B_ERR_NO_DEVICE};
   }
-  if (device < 0 || device >= n) {
+  if (device < 0 || device >= n || device >= 64) {
     set_error("device index out of range");
     throw Err{F5B_ERR_NO_DEVICE};
   }
-  cudaDeviceProp p;
-  F5B_CHECK_CUDA(cudaGetDeviceProperties(&p, device));
-  if (p.major != 10) {
-    set_error(std::string("device '") + p.name + "' is sm_" + std::to_string(p.major) + std::to_string(p.minor) +
+  std::lock_guard<std::mutex> lock(g_dev_mu);
+  DeviceInfo& d = g_dev[device];
+  if (!d.checked) {
+    cudaDeviceProp p;
+    F5B_CHECK_CUDA(cudaGetDeviceProperties(&p, device));
+    d.major = p.major;
+    d.minor = p.minor;
+    d.sm_count = p.multiProcessorCount;
+    d.name = p.name;
+    d.checked = true;
+  }
+  if (d.major != 10) {
+    set_error(std::string("device '") + d.name + "' is sm_" + std::to_string(d.major) + std::to_string(d.minor) +
               "; libf5b200 is built for sm_100a only");
     throw Err{F5B_ERR_NO_DEVICE};
   }
   F5B_CHECK_CUDA(cudaSetDevice(device));
+  return d;
 }
 
-static bool g_kernels_ready = false;
 DeviceCtx open_device(int device, int mode) {
-  device_check_throw(device);
+  DeviceInfo& d = device_check_throw(device);
   DeviceCtx c;
   c.device = device;
   c.mode = mode;
-  cudaDeviceProp p;
-  F5B_CHECK_CUDA(cudaGetDeviceProperties(&p, device));
-  c.sm_count = p.multiProcessorCount;
-  if (!g_kernels_ready) {
-    tc_init_kernels();
-    tc_attn_bwd_init_kernels();
-    tc_gemm_init_kernels();
-    simt_init_kernels();
-    g_kernels_ready = true;
+  c.sm_count = d.sm_count;
+  if (!d.kernels_ready) {  // per DEVICE: the dynamic shared-memory limits are attributes of a function on a device
+    std::lock_guard<std::mutex> lock(g_dev_mu);
+    if (!d.kernels_ready) {
+      tc_init_kernels();
+      tc_attn_bwd_init_kernels();
+      tc_gemm_init_kernels();
+      simt_init_kernels();
+      d.kernels_ready = true;
+    }
   }
   return c;
 }

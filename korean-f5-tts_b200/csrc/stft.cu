@@ -23,13 +23,15 @@ struct StftTables {
   float* fb = nullptr;    // [513, 100]
   int device = -1;
 };
-static StftTables g_tab;
+static StftTables g_tabs[64];  // one set per device, built on first use with that device current
 static std::mutex g_tab_mu;
 
 static const StftTables& tables_for(int device) {
   std::lock_guard<std::mutex> lk(g_tab_mu);
+  F5B_REQUIRE(device >= 0 && device < 64, "device index beyond the STFT table slots");
+  StftTables& g_tab = g_tabs[device];
   if (g_tab.device == device) return g_tab;
-  F5B_REQUIRE(g_tab.device == -1, "libf5b200 STFT tables are bound to one device per process");
+  F5B_CHECK_CUDA(cudaSetDevice(device));
   std::vector<float2> tw(512);
   std::vector<float> win(NFFT), fb((size_t)NBIN * NMEL);
   const double PI = 3.14159265358979323846;

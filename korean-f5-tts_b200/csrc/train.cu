@@ -143,6 +143,55 @@ colsum_final_kernel(const float* __restrict__ part, int chunks, int cols, float*
   for (int s = 0; s < chunks; ++s) acc += part[(long long)s * cols + j];
   out[j] = acc;
 }
+// 16-byte form of both kernels above: a CTA covers 256 columns (64 float4 lanes) of one segment of rows (a batch element
+// or a chunk) with FOUR row groups (rows r0 + g, r0 + g + 4, ...), each thread keeping two independent sums in flight;
+// the groups are added in order through shared memory -- one owner per output, fixed order, 4x the loads in flight.
+__global__ void __launch_bounds__(256)
+colsum_seg4_kernel(const float* __restrict__ X, const float* __restrict__ Y, int seg_rows, int rows_total, int cols,
+                   float* __restrict__ out, long long out_sstride) {
+  __shared__ float4 red[4][64];
+  const int q = threadIdx.x & 63, g = threadIdx.x >> 6, s = blockIdx.y;
+  const int c = (blockIdx.x * 64 + q) * 4;
+  const long long r0 = (long long)s * seg_rows;
+  const long long r1 = min((long long)rows_total, r0 + seg_rows);
+  float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+  if (c < cols) {
+    long long r = r0 + g;
+    for (; r + 4 < r1; r += 8) {
+      const float4 x0 = *reinterpret_cast<const float4*>(X + r * cols + c);
+      const float4 x1 = *reinterpret_cast<const float4*>(X + (r + 4) * cols + c);
+      if (Y) {
+        const float4 y0 = *reinterpret_cast<const float4*>(Y + r * cols + c);
+        const float4 y1 = *reinterpret_cast<const float4*>(Y + (r + 4) * cols + c);
+        a0.x = fmaf(x0.x, y0.x, a0.x); a0.y = fmaf(x0.y, y0.y, a0.y); a0.z = fmaf(x0.z, y0.z, a0.z); a0.w = fmaf(x0.w, y0.w, a0.w);
+        a1.x = fmaf(x1.x, y1.x, a1.x); a1.y = fmaf(x1.y, y1.y, a1.y); a1.z = fmaf(x1.z, y1.z, a1.z); a1.w = fmaf(x1.w, y1.w, a1.w);
+      } else {
+        a0.x += x0.x; a0.y += x0.y; a0.z += x0.z; a0.w += x0.w;
+        a1.x += x1.x; a1.y += x1.y; a1.z += x1.z; a1.w += x1.w;
+      }
+    }
+    if (r < r1) {
+      const float4 x0 = *reinterpret_cast<const float4*>(X + r * cols + c);
+      if (Y) {
+        const float4 y0 = *reinterpret_cast<const float4*>(Y + r * cols + c);
+        a0.x = fmaf(x0.x, y0.x, a0.x); a0.y = fmaf(x0.y, y0.y, a0.y); a0.z = fmaf(x0.z, y0.z, a0.z); a0.w = fmaf(x0.w, y0.w, a0.w);
+      } else {
+        a0.x += x0.x; a0.y += x0.y; a0.z += x0.z; a0.w += x0.w;
+      }
+    }
+  }
+  red[g][q] = make_float4(a0.x + a1.x, a0.y + a1.y, a0.z + a1.z, a0.w + a1.w);
+  __syncthreads();
+  if (g == 0 && c < cols) {
+    float4 t = red[0][q];
+#pragma unroll
+    for (int k = 1; k < 4; ++k) {
+      t.x += red[k][q].x; t.y += red[k][q].y; t.z += red[k][q].z; t.w += red[k][q].w;
+    }
+    float* o = out + (long long)s * out_sstride + c;
+    o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+  }
+}
 static thread_local float* g_colsum_scratch = nullptr;
 static thread_local size_t g_colsum_scratch_floats = 0;
 void colsum_set_scratch(float* p, size_t floats) {
@@ -156,12 +205,29 @@ float* colsum_scratch(size_t* floats) {
 void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
                   long long out_bstride) {
   constexpr int kChunks = 128;
+  const bool vec = cols % 4 == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0 &&
+                   (Y == nullptr || (reinterpret_cast<uintptr_t>(Y) & 15) == 0);
   if (batches == 1 && rows_per_batch >= 4096 && g_colsum_scratch != nullptr &&
       (size_t)kChunks * cols <= g_colsum_scratch_floats) {
     const int chunk = (rows_per_batch + kChunks - 1) / kChunks;
+    if (vec) {
+      const int chunks = (rows_per_batch + chunk - 1) / chunk;
+      colsum_seg4_kernel<<<dim3(cdiv(cols, 256), chunks), 256, 0, st>>>(X, Y, chunk, rows_per_batch, cols,
+                                                                       g_colsum_scratch, cols);
+      F5B_POST_LAUNCH();
+      colsum_final_kernel<<<cdiv(cols, 256), 256, 0, st>>>(g_colsum_scratch, chunks, cols, out);
+      F5B_POST_LAUNCH();
+      return;
+    }
     colsum_chunk_kernel<<<dim3(cdiv(cols, 256), kChunks), 256, 0, st>>>(X, Y, rows_per_batch, cols, chunk, g_colsum_scratch);
     F5B_POST_LAUNCH();
     colsum_final_kernel<<<cdiv(cols, 256), 256, 0, st>>>(g_colsum_scratch, kChunks, cols, out);
+    F5B_POST_LAUNCH();
+    return;
+  }
+  if (vec && rows_per_batch >= 64) {
+    colsum_seg4_kernel<<<dim3(cdiv(cols, 256), batches), 256, 0, st>>>(X, Y, rows_per_batch, batches * rows_per_batch,
+                                                                      cols, out, out_bstride);
     F5B_POST_LAUNCH();
     return;
   }

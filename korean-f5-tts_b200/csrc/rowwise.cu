@@ -2,6 +2,8 @@
 // One warp owns one row wherever a row statistic is needed (rows are 2-4 KB: the re-reads hit L1).
 #include "rowwise.h"
 
+#include <cstdlib>
+
 namespace f5b {
 
 static inline int ceil_div_ll(long long a, long long b) { return (int)((a + b - 1) / b); }
@@ -114,9 +116,14 @@ ln_mod_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int
 // Register-resident variant for d <= 1024: the row is read from memory once (8 float4 per lane).
 // LN_REG_ROWS rows (one per warp) per CTA (2-row CTAs, 940 of them at C2, measured the same step time as 8-row ones).
 static constexpr int LN_REG_ROWS = 8;
+static constexpr long long LN_STREAM_ROWS = 8192;  // from here on (16-bit outputs, d = 1024) the streaming form is used
 
-template <typename T>
-__global__ void __launch_bounds__(32 * LN_REG_ROWS)
+// kPrefetchMod: hold the modulation vectors in registers across the dependency wait (batch-1 latency path, 113
+// registers, 2 CTAs / SM); otherwise they are read in the store loop (L1 / L2 hits: one utterance's rows share them) so
+// that 4 CTAs / SM keep twice the row loads in flight -- the streaming form for large M.  Same arithmetic, same bits
+// (tests/test_gpu_fullsize.py compares the two).
+template <typename T, bool kPrefetchMod>
+__global__ void __launch_bounds__(32 * LN_REG_ROWS, kPrefetchMod ? 2 : 4)
 ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M, int d, const float* __restrict__ mul,
                   const float* __restrict__ add, float mul_off, long long vec_bstride, int rows_per_batch, int bmod,
                   float eps) {
@@ -132,13 +139,15 @@ ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M,
   const float* ad = add ? add + b * vec_bstride : nullptr;
   float4 buf[8], g[8], h[8];
   // the modulation vectors are per-call tables (not written inside the step chain): fetched before the dependency wait
+  if (kPrefetchMod) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int c = i * 128 + lane * 4;
-    if (c < d) {
-      g[i] = mu ? __ldg(reinterpret_cast<const float4*>(mu + c))
-                : make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
-      h[i] = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
+    for (int i = 0; i < 8; ++i) {
+      const int c = i * 128 + lane * 4;
+      if (c < d) {
+        g[i] = mu ? __ldg(reinterpret_cast<const float4*>(mu + c))
+                  : make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
+        h[i] = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
+      }
     }
   }
   pdl_wait();
@@ -169,6 +178,11 @@ ln_mod_reg_kernel(const float* __restrict__ x, T* __restrict__ out, long long M,
     const int c = i * 128 + lane * 4;
     if (c < d) {
       const float4 v = buf[i];
+      if (!kPrefetchMod) {
+        g[i] = mu ? __ldg(reinterpret_cast<const float4*>(mu + c))
+                  : make_float4(1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off, 1.0f - mul_off);
+        h[i] = ad ? __ldg(reinterpret_cast<const float4*>(ad + c)) : make_float4(0, 0, 0, 0);
+      }
       RowOut<T>::st(orow, c, d, (v.x - mean) * rstd * (mul_off + g[i].x) + h[i].x,
                     (v.y - mean) * rstd * (mul_off + g[i].y) + h[i].y,
                     (v.z - mean) * rstd * (mul_off + g[i].z) + h[i].z,
@@ -182,8 +196,17 @@ template <typename T>
 void ln_mod(cudaStream_t st, const float* x, T* out, long long M, int d, const float* mul, const float* add,
             float mul_off, long long vec_bstride, int rows_per_batch, int bmod, float eps) {
   F5B_REQUIRE(d % 4 == 0, "LayerNorm width must be a multiple of 4");
-  if (d <= 1024)
-    launch_pdl_id(4, ln_mod_reg_kernel<T>, dim3(ceil_div_ll(M, LN_REG_ROWS)), dim3(32 * LN_REG_ROWS), 0, st, x, out, M, d, mul, add, mul_off,
+  // The streaming form is opt-in (F5B_LN_STREAM=1) and serves the 16-bit mode at the model width only: bit-identical to
+  // the latency form (tests/test_gpu_fullsize.py), but its gain on the C3 job measured inside the run-to-run noise
+  // (13.49 vs 13.79 s, two runs each) and none on the training step, so the default stays the kernel every parity test
+  // was written against.
+  const char* env = std::getenv("F5B_LN_STREAM");
+  const bool want_stream = env ? std::atoi(env) != 0 : false;
+  if (d == 1024 && sizeof(T) == 2 && want_stream && M >= LN_STREAM_ROWS)
+    launch_pdl_id(4, ln_mod_reg_kernel<T, false>, dim3(ceil_div_ll(M, LN_REG_ROWS)), dim3(32 * LN_REG_ROWS), 0, st, x, out, M, d, mul, add, mul_off,
+               vec_bstride, rows_per_batch, bmod < 1 ? 1 : bmod, eps);
+  else if (d <= 1024)
+    launch_pdl_id(4, ln_mod_reg_kernel<T, true>, dim3(ceil_div_ll(M, LN_REG_ROWS)), dim3(32 * LN_REG_ROWS), 0, st, x, out, M, d, mul, add, mul_off,
                vec_bstride, rows_per_batch, bmod < 1 ? 1 : bmod, eps);
   else
     ln_mod_kernel<T><<<ceil_div_ll(M, 8), 256, 0, st>>>(x, out, M, d, mul, add, mul_off, vec_bstride, rows_per_batch,

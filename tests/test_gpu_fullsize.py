@@ -204,3 +204,27 @@ def test_full_pipeline_waveform_snr():
     s = snr_db(wavs["fp32"], wavs["bf16"])
     print(f"pipeline waveform SNR 16-bit vs fp32: {s:.1f} dB")
     assert s >= 40.0
+
+
+def test_streaming_layernorm_gives_the_bits_of_the_latency_form(monkeypatch):
+    """With F5B_LN_STREAM=1 the AdaLN LayerNorm runs in its streaming form from 8192 rows on (16-bit mode, model width
+    1024: modulation vectors read in the store loop, 4 CTAs per SM).  Same arithmetic in the same order: one CFG-doubled evaluation over
+    9 x 1000 rows (18 000 with both branches) with the form forced on equals the evaluation with it forced off bit for
+    bit, with per-utterance time steps (different modulation vectors per batch element) and key masks."""
+    cfg = O.ArchCfg(dim=1024, depth=2, heads=16, ff_mult=2, text_dim=512, conv_layers=1, attn_mask_enabled=True)
+    sd = O.synth_backbone_weights(cfg, seed=4)
+    cfm = build_cfm(cfg, sd, "bf16")
+    g = torch.Generator().manual_seed(3)
+    B, N = 9, 1000
+    x = torch.randn(B, N, 100, generator=g).cuda()
+    cond = torch.randn(B, N, 100, generator=g).cuda()
+    text = torch.randint(0, 50, (B, 60), generator=g).cuda()
+    t = torch.rand(B, generator=g)
+    lens = torch.tensor([1000, 990, 900, 800, 700, 640, 513, 512, 300])
+    mask = (torch.arange(N)[None, :] < lens[:, None]).cuda()
+    outs = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("F5B_LN_STREAM", flag)
+        outs[flag] = cfm.transformer(x, cond, text, t, mask=mask, cfg_infer=True).cpu()
+    assert torch.isfinite(outs["0"]).all() and float(outs["0"].abs().max()) > 0.1
+    assert torch.equal(outs["0"], outs["1"])

@@ -316,14 +316,26 @@ tc_attn_dkv_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
     const uint32_t tS = tmem_base + lane_off, tP = tmem_base + C_DP + lane_off;
     const long long sbase = ((long long)b * heads + h) * rows;
+    // per-query statistics of the step's KB queries: loaded from global memory ONE STEP AHEAD into registers (the
+    // profile showed the load -> shared store -> barrier of the current step as the largest stall of the kernel), then
+    // published through shared memory (double-buffered; the named barrier orders writers and readers)
+    float nxt_lse = INFINITY, nxt_D = 0.0f;
+    if (row < KB && nq > 0 && row < rows) {
+      nxt_lse = lse2[sbase + row];
+      nxt_D = Dr[sbase + row];
+    }
     for (int i = 0; i < nq; ++i) {
-      {  // this block's per-query statistics -> smem (double-buffered; the named barrier orders writers and readers)
+      {
         if (row < KB) {
-          const int qr = i * KB + row;
-          s_lse[(i & 1) * KB + row] = qr < rows ? lse2[sbase + qr] : INFINITY;
-          s_D[(i & 1) * KB + row] = qr < rows ? Dr[sbase + qr] : 0.0f;
+          s_lse[(i & 1) * KB + row] = nxt_lse;
+          s_D[(i & 1) * KB + row] = nxt_D;
         }
         named_bar_sync(1, 128);
+        if (row < KB && i + 1 < nq) {
+          const int qr = (i + 1) * KB + row;
+          nxt_lse = qr < rows ? lse2[sbase + qr] : INFINITY;
+          nxt_D = qr < rows ? Dr[sbase + qr] : 0.0f;
+        }
       }
       const float4* l4 = reinterpret_cast<const float4*>(s_lse + (i & 1) * KB);
       const float4* d4 = reinterpret_cast<const float4*>(s_D + (i & 1) * KB);

@@ -11,7 +11,16 @@ from f5b200 import _lib as L  # noqa: E402
 
 ms = C.c_float()
 what = sys.argv[1] if len(sys.argv) > 1 else "attn"
-if what == "attn":
+if what == "attn_bwd":  # the training step's attention backward at the C5 sequence length (4 of the 40 utterances)
+    B, N, H = 4, 960, 16
+    g = torch.Generator().manual_seed(0)
+    qkv = torch.randn(B * N, 3 * H * 64, generator=g).cuda()
+    d_o = torch.randn(B * N, H * 64, generator=g).cuda()
+    out = torch.empty(B * N, 3 * H * 64, device="cuda")
+    for _ in range(2):
+        L.check(L.lib().f5b_op_attention_bwd(1, qkv.data_ptr(), d_o.data_ptr(), None, B, N, H, out.data_ptr(), 0, 0))
+    print("attention backward", B, N, H, float(out.abs().max()))
+elif what == "attn":
     for rows in (940, 2801):
         L.check(L.lib().f5b_op_time(1, rows, 16, 2, 2, C.byref(ms), 0, 0))
         print("attention", rows, ms.value * 1e3, "us")

@@ -156,26 +156,31 @@ gconv_wgrad_kernel(const float* __restrict__ dz, const float* __restrict__ x, in
 __global__ void __launch_bounds__(256)
 gconv_wgrad64_kernel(const float* __restrict__ dz, const float* __restrict__ x, int batches, int rows, int C, int taps,
                      const int* __restrict__ row_len, float* __restrict__ dw) {
-  __shared__ float Gs[16][64 + 1], Xs[16][64 + 1];
+  // 32-row tiles, rows of 64 floats (16-byte aligned): each thread reads its 4 + 4 operands of a row as two 128-bit
+  // shared loads (the 65-float padded rows of the first version made them eight scalar loads per 16 FMAs)
+  __shared__ __align__(16) float Gs[32][64], Xs[32][64];
   const int g = blockIdx.x, tap = blockIdx.y, pad = taps / 2;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   float acc[4][4] = {};
   for (int b = 0; b < batches; ++b) {
     const int len = row_len ? row_len[b] : rows;
-    for (int t0 = 0; t0 < rows; t0 += 16) {
-      for (int e = tid; e < 16 * 64; e += 256) {
-        const int r = e >> 6, c = e & 63, t = t0 + r, tt = t + tap - pad;
-        Gs[r][c] = t < rows ? dz[((long long)b * rows + t) * C + g * 64 + c] : 0.0f;
-        Xs[r][c] = (t < rows && tt >= 0 && tt < len) ? x[((long long)b * rows + tt) * C + g * 64 + c] : 0.0f;
+    for (int t0 = 0; t0 < rows; t0 += 32) {
+      for (int e = tid; e < 32 * 16; e += 256) {  // one float4 per thread and pass
+        const int r = e >> 4, c = (e & 15) * 4, t = t0 + r, tt = t + tap - pad;
+        float4 gv = make_float4(0.f, 0.f, 0.f, 0.f), xv = gv;
+        if (t < rows) {
+          gv = *reinterpret_cast<const float4*>(dz + ((long long)b * rows + t) * C + g * 64 + c);
+          if (tt >= 0 && tt < len) xv = *reinterpret_cast<const float4*>(x + ((long long)b * rows + tt) * C + g * 64 + c);
+        }
+        *reinterpret_cast<float4*>(&Gs[r][c]) = gv;
+        *reinterpret_cast<float4*>(&Xs[r][c]) = xv;
       }
       __syncthreads();
-#pragma unroll
-      for (int r = 0; r < 16; ++r) {
-        float a[4], v[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) a[i] = Gs[r][ty * 4 + i];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) v[j] = Xs[r][tx * 4 + j];
+#pragma unroll 8
+      for (int r = 0; r < 32; ++r) {
+        const float4 av = *reinterpret_cast<const float4*>(&Gs[r][ty * 4]);
+        const float4 vv = *reinterpret_cast<const float4*>(&Xs[r][tx * 4]);
+        const float a[4] = {av.x, av.y, av.z, av.w}, v[4] = {vv.x, vv.y, vv.z, vv.w};
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll

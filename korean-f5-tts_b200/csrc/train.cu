@@ -467,8 +467,30 @@ rope_qk_kernel(float* __restrict__ qkv, long long M, int inner, int rows_per_bat
   x[0] = a * t.x - c * sn;
   x[1] = c * t.x + a * sn;
 }
+// two pairs (one float4 of x, one float4 of the table) per thread
+__global__ void __launch_bounds__(256)
+rope_qk4_kernel(float* __restrict__ qkv, long long M, int inner, int rows_per_batch, int rope_heads,
+                const float* __restrict__ cs, float dir) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;  // one thread per (row, q-or-k, 4 columns)
+  const int quads = inner / 4;
+  if (i >= M * 2 * quads) return;
+  const long long m = i / (2 * quads);
+  const int r = (int)(i - m * 2 * quads), part = r / quads, col = (r - part * quads) * 4;
+  if ((col >> 6) >= rope_heads) return;
+  const int pos = (int)(m % rows_per_batch);
+  const float4 t = *reinterpret_cast<const float4*>(cs + (long long)pos * 64 + (col & 63));
+  float4* x = reinterpret_cast<float4*>(qkv + m * 3 * inner + (long long)part * inner + col);
+  const float4 v = *x;
+  const float s0 = dir * t.y, s1 = dir * t.w;
+  *x = make_float4(v.x * t.x - v.y * s0, v.y * t.x + v.x * s0, v.z * t.z - v.w * s1, v.w * t.z + v.z * s1);
+}
 void rope_qk(cudaStream_t st, float* qkv, long long M, int inner, int rows_per_batch, int rope_heads, const float* cs,
              float dir) {
+  if (inner % 4 == 0 && al16(qkv) && al16(cs)) {
+    rope_qk4_kernel<<<cdiv(M * (inner / 2), 256), 256, 0, st>>>(qkv, M, inner, rows_per_batch, rope_heads, cs, dir);
+    F5B_POST_LAUNCH();
+    return;
+  }
   rope_qk_kernel<<<cdiv(M * inner, 256), 256, 0, st>>>(qkv, M, inner, rows_per_batch, rope_heads, cs, dir);
   F5B_POST_LAUNCH();
 }

@@ -405,8 +405,12 @@ embed_bwd_kernel(const float* __restrict__ dte, const long long* __restrict__ te
   if (i >= table_rows * td) return;
   const int v = i / td, c = i - v * td;
   float acc = 0.0f;
+  // rows at or beyond nt carry the filler token 0 and count as padding: they reach row 0 of the table only, and only
+  // when padding is not masked out -- every other (v, c) stops at the text length (170 instead of ~1000 rows)
+  const bool filler_counts = v == 0 && !(masked_fill_applies && mask_padding);
   for (int b = 0; b < B; ++b) {
-    const int len = row_len ? row_len[b] : rows;
+    int len = row_len ? row_len[b] : rows;
+    if (!filler_counts && len > nt) len = nt;
     for (int pos = 0; pos < len; ++pos) {
       long long tok = pos < nt ? text[(long long)b * nt + pos] + 1 : 0;
       if (tok < 0 || tok >= table_rows) tok = 0;

@@ -21,8 +21,9 @@ struct DeviceCtx {
 // Owns cudaMalloc'd blocks; everything is released together.
 // Replay: code that allocates a deterministic sequence of buffers (the plan's weight packing, the training step's
 // workspace) can be run again over the SAME blocks -- begin_replay() rewinds, alloc() then hands out the existing
-// blocks in order (a block whose size no longer matches is replaced, further requests are appended), so a repeated
-// call costs no cudaMalloc / cudaFree (each of which synchronises the device).
+// blocks in order (a block that is too small is replaced by a larger one, further requests are appended), so a repeated
+// call costs no cudaMalloc / cudaFree (each of which synchronises the device) and batches of changing shape settle on
+// the largest sizes seen.
 class Arena {
  public:
   ~Arena() { release(); }

@@ -38,8 +38,8 @@ void* Arena::alloc(size_t bytes) {
   if (b == 0) b = 256;
   if (replay_ != (size_t)-1 && replay_ < blocks_.size()) {
     const size_t i = replay_++;
-    if (sizes_[i] == b) return blocks_[i];
-    F5B_CHECK_CUDA(cudaFree(blocks_[i]));  // the sequence changed shape here: replace this block
+    if (sizes_[i] >= b) return blocks_[i];  // grow-only: a smaller request (a shorter batch) reuses the larger block
+    F5B_CHECK_CUDA(cudaFree(blocks_[i]));   // the sequence needs more here than ever before: replace this block
     blocks_[i] = nullptr;
     total_ -= sizes_[i];
     sizes_[i] = 0;

@@ -114,3 +114,28 @@ def test_train_step_matches_torch_adamw_on_the_oracle():
     worst_ema = max(max_abs(e["ema_model.transformer." + k], v) / max(float(v.abs().max()), 1e-8) for k, v in ema.items())
     print(f"two AdamW steps: parameters within {worst:.2e}, EMA within {worst_ema:.2e} (relative to max|w|) of torch.optim.AdamW")
     assert worst <= 1e-4 and worst_ema <= 1e-4
+
+
+def test_step_workspace_survives_changing_batch_shapes():
+    """The training step's workspace is kept by the plan and handed out again on the next call (grow-only): batches of
+    changing shape -- what the reference's frame-budget batch sampler produces -- give the bits they give on a fresh
+    model, whether the call before was larger or smaller."""
+    cfg = O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2, attn_mask_enabled=True)
+    sd = O.synth_backbone_weights(cfg, seed=3)
+    shapes = [(2, 48), (3, 80), (1, 33), (3, 80), (2, 48)]
+    cases = {}
+    for b, n in set(shapes):
+        x1, text = O.synth_inputs(n, n, 9, batch=b, seed=b * 100 + n)
+        lens = torch.tensor([n - 3 * i for i in range(b)])
+        cases[(b, n)] = (x1.cuda(), text.cuda(), lens.cuda(), _draws(O.draw_loss_randoms(x1, 7)))
+    fresh = {}
+    for key, (x1, text, lens, d) in cases.items():
+        loss, g = build_cfm(cfg, sd, "fp32").tail_gradients(x1, text, lens=lens, draws=d)
+        fresh[key] = (loss.cpu(), {k: v.cpu() for k, v in g.items()})
+    cfm = build_cfm(cfg, sd, "fp32")
+    for key in shapes:
+        x1, text, lens, d = cases[key]
+        loss, g = cfm.tail_gradients(x1, text, lens=lens, draws=d)
+        assert torch.equal(loss.cpu(), fresh[key][0])
+        for k, v in g.items():
+            assert torch.equal(v.cpu(), fresh[key][1][k]), (key, k)

@@ -291,3 +291,31 @@ def test_two_threads_share_one_plan():
     for n in jobs:
         for out in got[n]:
             assert torch.equal(out, alone[n])
+
+
+def test_refresh_plan_repacks_weights_under_cached_graphs():
+    """`DiT.refresh_plan()` (f5b_plan_refresh) after the parameters were changed behind torch's back -- what TrainStep's
+    fused AdamW does -- re-packs the weights into the plan's existing buffers: the sampling graph captured BEFORE the
+    change is replayed on the new weights and gives the bits of a model built from them."""
+    cond, text = O.synth_inputs(60, 20, 7, seed=1)
+    y0 = torch.randn(1, 60, 100, generator=torch.Generator().manual_seed(3))
+    kw = dict(duration=60, steps=4, cfg_strength=2.0, sway_sampling_coef=-1.0)
+    for precision in ("fp32", "bf16"):
+        cfg = (O.ArchCfg(dim=128, depth=2, heads=2, ff_mult=2, text_dim=64, conv_layers=2) if precision == "fp32" else
+               O.ArchCfg(dim=1024, depth=1, heads=16, ff_mult=2, text_dim=512, conv_layers=1))  # 16-bit mode: model width
+        sd = O.synth_backbone_weights(cfg, seed=2)
+        sd2 = {k: (v * 1.05 + 0.01 if v.is_floating_point() and "inv_freq" not in k else v) for k, v in sd.items()}
+        cfm = build_cfm(cfg, sd, precision)
+        a1, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)
+        a2, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)  # graph replay
+        assert torch.equal(a1, a2)
+        with torch.no_grad():
+            for name, p in cfm.transformer.named_parameters():
+                p.data.copy_(sd2[name].to(p.device))  # .data: no version bump, the plan cannot see it
+        stale, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)
+        assert torch.equal(stale, a1)  # still the old weights: nothing told the plan
+        cfm.transformer.refresh_plan()
+        got, _ = cfm.sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)
+        want, _ = build_cfm(cfg, sd2, precision).sample(cond=cond.cuda(), text=text.cuda(), y0=y0, **kw)
+        assert not torch.equal(got, a1)
+        assert torch.equal(got, want), precision

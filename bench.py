@@ -318,17 +318,18 @@ def c3_lengths():
 
 def run_c3(cfm, voc, dev, stream, rank: int, world: int, pk: dict) -> dict:
     """STRONG scaling of one fixed job: 256 variable-length utterances (padded masks, attn_mask_enabled), NFE 32, CFG
-    2.0, Vocos; the request list is sharded over the ranks by an attention-aware LPT rule (f5b200/sharding.py; the
-    reference shards its request list with accelerate's split_between_processes, eval/eval_infer_batch.py:181) and each
-    rank runs its shard as length-sorted micro-batches -- no collective on the data path.  Reported: the job's device
+    2.0, Vocos; the request list is cut into length-sorted micro-batches and the batches are dealt to the ranks by an
+    attention-aware LPT rule (f5b200/sharding.py:plan_job; the reference shards its request list with accelerate's
+    split_between_processes, eval/eval_infer_batch.py:181) -- no collective on the data path.  Reported: the job's device
     time = max over ranks, per-rank times and their imbalance, aggregate generated-audio seconds per second."""
     import torch.distributed as dist
 
-    from f5b200.sharding import micro_batches, my_shard
+    from f5b200.sharding import plan_job
 
     frames, n_ref = c3_lengths()
-    mine = my_shard(frames, rank, world)
-    groups = micro_batches(mine, frames, max_rows=C3_MAX_ROWS, max_batch=64)
+    plan, rows_used = plan_job(frames, world, max_rows=C3_MAX_ROWS, max_batch=64)  # batches first, then dealt to ranks
+    groups = sorted(plan[rank], key=lambda g: -max(frames[i] for i in g))
+    mine = [i for g in groups for i in g]
 
     def inputs(grp):
         b, n = len(grp), max(frames[i] for i in grp)
@@ -380,8 +381,8 @@ def run_c3(cfm, voc, dev, stream, rank: int, world: int, pk: dict) -> dict:
     gen_total = float(allst[:, 1].sum())
     flops = sum(flops_per_eval(n=f) for f in frames) * C3_NFE
     return {"workload": f"C3: {MODEL}, {C3_UTTERANCES} utterances of 3-20 s ({sum(frames)} frames, prompt {n_ref}), NFE "
-                        f"{C3_NFE}, CFG {CFG} doubled batch, key masks on, Vocos; request-sharded x{world} (LPT), "
-                        f"micro-batches <= {C3_MAX_ROWS} padded frames, eager launches",
+                        f"{C3_NFE}, CFG {CFG} doubled batch, key masks on, Vocos; length-sorted micro-batches <= "
+                        f"{rows_used} padded frames dealt to x{world} ranks (LPT over batches), eager launches",
             "scaling": "strong", "device_s": round(t_job, 4), "per_rank_device_s": [round(x, 4) for x in t_all],
             "imbalance_max_over_mean": round(t_job / (sum(t_all) / len(t_all)), 4),
             "utterances_per_rank": [int(x) for x in allst[:, 2].tolist()],

@@ -2,8 +2,9 @@
 collective runs on the data path (the reference shards the same way with `accelerator.split_between_processes`,
 src/f5_tts/eval/eval_infer_batch.py:181, and `DistributedSampler`, runtime/triton_trtllm/benchmark.py:340-341).
 
-Unlike the reference's contiguous split, shards are balanced by an attention-aware cost and each shard is cut into
-length-sorted micro-batches so padding waste inside a batch stays small."""
+Unlike the reference's contiguous split, work is balanced by an attention-aware cost.  A job whose whole request list
+is known (`plan_job`) is cut into length-sorted micro-batches first and the batches are dealt to the ranks; a rank that
+only knows its own utterances (`my_shard`) cuts its shard into micro-batches itself."""
 from __future__ import annotations
 
 from typing import List, Sequence
@@ -51,6 +52,39 @@ def micro_batches(indices: Sequence[int], lengths: Sequence[int], max_rows: int,
     if cur:
         out.append(cur)
     return out
+
+
+def batch_cost(group: Sequence[int], lengths: Sequence[int], **cost_kw) -> float:
+    """Cost of one micro-batch: every row is computed at the padded length."""
+    return len(group) * request_cost(max(lengths[i] for i in group), **cost_kw)
+
+
+def plan_job(lengths: Sequence[int], world_size: int, max_rows: int = 16384, max_batch: int = 64,
+             max_waste: float = 0.05, **cost_kw):
+    """BATCH FIRST, SHARD SECOND: the whole request list is cut into length-sorted micro-batches (`micro_batches`), then
+    the BATCHES are dealt to the ranks longest-processing-time first.  Sharding utterances first (`shard_requests` +
+    `micro_batches` per rank) leaves every rank with a thin slice of each length class -- on 8 GPUs the C3 job ran as
+    12-14 calls of ~2.5 utterances per rank, at 13 % lower tensor throughput than the 16 k-row batches of one GPU; dealt
+    as whole batches the ranks keep the single-GPU batch sizes and padding.  With few batches per rank the balance depends
+    on the batch size, so a few row limits are tried and the one with the smallest estimated finishing time is kept (a
+    smaller limit is charged 3 % per halving for its lower kernel efficiency).
+    Returns (per-rank list of micro-batches, the row limit used).  Deterministic: every rank computes the same plan."""
+    import math
+
+    best = None
+    for rows in sorted({max_rows, max_rows * 7 // 8, max_rows * 3 // 4, max_rows * 5 // 8, max_rows // 2}, reverse=True):
+        groups = micro_batches(range(len(lengths)), lengths, rows, max_batch, max_waste)
+        order = sorted(range(len(groups)), key=lambda k: (-batch_cost(groups[k], lengths, **cost_kw), k))
+        loads = [0.0] * world_size
+        plan: List[List[List[int]]] = [[] for _ in range(world_size)]
+        for k in order:
+            r = min(range(world_size), key=lambda q: (loads[q], q))
+            plan[r].append(groups[k])
+            loads[r] += batch_cost(groups[k], lengths, **cost_kw)
+        est = max(loads) / (1.0 - 0.03 * math.log2(max_rows / rows))
+        if best is None or est < best[0] * (1.0 - 1e-9):
+            best = (est, plan, rows)
+    return best[1], best[2]
 
 
 def my_shard(lengths: Sequence[int], rank: int, world_size: int, **cost_kw) -> List[int]:

@@ -73,6 +73,12 @@ void f5b_plan_destroy(f5b_plan* plan);
  * creation) into the plan's existing device buffers.  No allocation; workspace and graphs stay valid.  Synchronous:
  * waits for `stream` (the stream the update ran on) first and returns when the new weights are in place. */
 int f5b_plan_refresh(f5b_plan* plan, const f5b_tensor* weights, int32_t n_weights, void* stream);
+/* Grow the plan's workspace NOW for a batch of B utterances of N frames, nt text tokens, `steps` ODE steps (the
+ * capacities are kept per quantity and never shrink).  A caller that knows the shapes of a whole job -- the chunks of
+ * infer_batch_process (infer/utils_infer.py:500-770), the micro-batches of an evaluation run
+ * (eval/eval_infer_batch.py) -- reserves them up front, so no call inside the job re-allocates (a re-allocation
+ * synchronises the device and drops the cached graphs).  f5b_vocos_reserve does the same for Vocos (B x T frames). */
+int f5b_plan_reserve(f5b_plan* plan, int32_t B, int32_t N, int32_t nt, int32_t steps);
 
 /* Replaces the ODE part of CFM.sample (model/cfm.py:160-219): text-embedding cache, EPSS/sway grid consumption,
  * CFG-doubled backbone evaluations, Euler updates.  Inputs are what cfm.py:104-216 builds on the host:
@@ -171,6 +177,7 @@ int f5b_vocos_decode(f5b_vocos* v, const float* mel, int32_t B, int32_t T, float
  * applies at ITS end; wav [B, (T-1)*256], row b valid up to (lens[b]-1)*256 samples, zeros after. */
 int f5b_vocos_decode_varlen(f5b_vocos* v, const float* mel, const int32_t* lens, int32_t B, int32_t T, float* wav,
                             int32_t mem, void* stream);
+int f5b_vocos_reserve(f5b_vocos* v, int32_t B, int32_t T);
 
 /* Kernel-level entry points used by the parity tests and the roofline benchmark (device pointers only).
  *   gemm:      out[M,N] = act(A[M,K] W[N,K]^T + bias); mode selects fp32 SIMT or bf16 tcgen05 (inputs fp32, converted)

@@ -191,6 +191,18 @@ void f5b_vocos_destroy(f5b_vocos* v) {
 
 // mel [B, 100, T] (+ lens [B] int32 or NULL: row b holds lens[b] <= T frames, zero padding applies at ITS end) ->
 // wav [B, (T - 1) * 256], row b valid up to (lens[b] - 1) * 256 samples, zeros after.  Device buffers: asynchronous.
+int f5b_vocos_reserve(f5b_vocos* v, int32_t B, int32_t T) {
+  try {
+    F5B_REQUIRE(v && B > 0 && T > 1, "bad argument");
+    F5B_CHECK_CUDA(cudaSetDevice(v->ctx.device));
+    std::lock_guard<std::mutex> lock(v->mu);
+    v->ensure((long long)B * T, B);
+  } catch (const f5b::Err& e) {
+    return e.code;
+  }
+  return F5B_OK;
+}
+
 int f5b_vocos_decode_varlen(f5b_vocos* v, const float* mel, const int32_t* lens, int32_t B, int32_t T, float* wav,
                             int32_t mem, void* stream) {
   try {

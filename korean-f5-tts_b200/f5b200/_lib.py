@@ -66,6 +66,8 @@ _SIGNATURES = {
                               C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "f5b_op_attention": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                    C.c_int32, C.c_void_p]),
+    "f5b_plan_reserve": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]),
+    "f5b_vocos_reserve": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "f5b_plan_refresh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     "f5b_op_attention_bwd": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                        C.c_void_p, C.c_int32, C.c_void_p]),

@@ -180,6 +180,13 @@ class _PlanBackbone(nn.Module):
         self._plan_sig = sig
         return handle
 
+    def reserve(self, shapes, steps: int = 32):
+        """Grow the workspace up front for every (batch, frames, text tokens) shape of a job, so that no call inside the
+        job re-allocates (capacities are per quantity and monotone: f5b_plan_reserve)."""
+        plan = self.plan()
+        for b, n, nt in shapes:
+            _lib.check(_lib.lib().f5b_plan_reserve(plan, int(b), int(n), int(max(nt, 1)), int(steps)))
+
     def refresh_plan(self):
         """After parameters were updated in place behind torch's back (TrainStep's fused AdamW writes the flat buffer
         the parameters are views of): re-pack the weights into the existing plan (no allocation, graphs stay valid)."""

@@ -175,6 +175,16 @@ def infer_batch_process(ref_audio, ref_text: str, gen_text_batches: Iterable[str
             by_len.setdefault(eff[i], []).append(i)
         groups = [g[k:k + max_batch] for g in by_len.values() for k in range(0, len(g), max_batch)]
 
+    # every shape of the request is known here: reserve the workspaces once, so that no micro-batch re-allocates (a
+    # re-allocation synchronises the device and drops the cached graphs) -- objects without the method are left alone
+    if len(groups) > 1:
+        tr = getattr(model_obj, "transformer", None)
+        if hasattr(tr, "reserve"):
+            tr.reserve([(len(g), max(eff[i] for i in g), max(len(ids[i]) for i in g)) for g in groups], steps=nfe_step)
+        if hasattr(vocoder, "reserve"):
+            for g in groups:
+                vocoder.reserve(len(g), max(max(eff[i] for i in g) - ref_audio_len, 2))
+
     def launch(g):
         """Enqueue one micro-batch: sample() + ONE Vocos call over its rows (per-row lengths: each row is decoded as if
         alone) + device -> pinned-host copies.  Nothing here waits for the GPU (the C ABI is asynchronous for device

@@ -101,6 +101,10 @@ class Vocos(nn.Module):
 
     forward = decode
 
+    def reserve(self, batch: int, frames: int):
+        """Grow the workspace up front for a decode of `batch` x `frames` (monotone capacity: f5b_vocos_reserve)."""
+        _lib.check(_lib.lib().f5b_vocos_reserve(self.handle(), int(batch), int(frames)))
+
 
 def load_vocoder(vocoder_name="vocos", is_local=False, local_path="", device="cuda", hf_cache_dir=None, *,
                  precision: str | None = None, allow_uninitialized: bool = False):

@@ -20,6 +20,11 @@ if what == "attn_bwd":  # the training step's attention backward at the C5 seque
     for _ in range(2):
         L.check(L.lib().f5b_op_attention_bwd(1, qkv.data_ptr(), d_o.data_ptr(), None, B, N, H, out.data_ptr(), 0, 0))
     print("attention backward", B, N, H, float(out.abs().max()))
+elif what == "gemm_big":  # the CTA-pair tiles at the training step's row count (M = 38 400) and at a C3 batch (32 768)
+    for m in (38400, 32768):
+        for which, n, k in ((0, 3072, 1024), (0, 2048, 1024), (4, 1024, 2048)):
+            L.check(L.lib().f5b_op_time(which, m, n, k, 2, C.byref(ms), 0, 0))
+            print("gemm", m, n, k, ms.value * 1e3, "us", 2.0 * m * n * k / ms.value / 1e9, "TFLOP/s")
 elif what == "attn":
     for rows in (940, 2801):
         L.check(L.lib().f5b_op_time(1, rows, 16, 2, 2, C.byref(ms), 0, 0))

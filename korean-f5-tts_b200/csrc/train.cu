@@ -273,6 +273,7 @@ void ln_mod_fwd_save(cudaStream_t st, const float* x, long long M, int d, const 
   F5B_POST_LAUNCH();
 }
 
+static inline bool al16f(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 __global__ void __launch_bounds__(256)
 ln_mod_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, const float* __restrict__ rstd,
                   long long M, int d, const float* __restrict__ scale, long long vec_bstride, int rows_per_batch,
@@ -295,10 +296,62 @@ ln_mod_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, 
     dx[m * d + c] = accumulate ? dx[m * d + c] + v : v;
   }
 }
+// Register-resident form for d = 128 k <= 1024 (the row of dy and of xhat is read ONCE, 16 bytes per lane and access):
+//   dx = (resid ? resid : 0) + rstd * (g - mean(g) - xhat * mean(g xhat)),  g = dy * (1 + scale[b])
+// `resid` may alias dx (accumulate in place) or be another buffer (the residual branch's gradient: no copy needed first).
+__global__ void __launch_bounds__(256)
+ln_mod_bwd4_kernel(const float* __restrict__ dy, const float* __restrict__ xhat, const float* __restrict__ rstd,
+                   long long M, int d, const float* __restrict__ scale, long long vec_bstride, int rows_per_batch,
+                   const float* resid, float* dx) {
+  const long long m = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (m >= M) return;
+  const float* sc = scale + (m / rows_per_batch) * vec_bstride;
+  float4 g[8], h[8];
+  float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < d) {
+      const float4 a = *reinterpret_cast<const float4*>(dy + m * d + c);
+      const float4 s = *reinterpret_cast<const float4*>(sc + c);
+      h[i] = *reinterpret_cast<const float4*>(xhat + m * d + c);
+      g[i] = make_float4(a.x * (1.0f + s.x), a.y * (1.0f + s.y), a.z * (1.0f + s.z), a.w * (1.0f + s.w));
+      s1 += (g[i].x + g[i].y) + (g[i].z + g[i].w);
+      s2 += (g[i].x * h[i].x + g[i].y * h[i].y) + (g[i].z * h[i].z + g[i].w * h[i].w);
+    }
+  }
+  const float m1 = warp_sum(s1) / d, m2 = warp_sum(s2) / d, r = rstd[m];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int c = i * 128 + lane * 4;
+    if (c < d) {
+      float4 v = make_float4(r * (g[i].x - m1 - h[i].x * m2), r * (g[i].y - m1 - h[i].y * m2),
+                             r * (g[i].z - m1 - h[i].z * m2), r * (g[i].w - m1 - h[i].w * m2));
+      if (resid != nullptr) {
+        const float4 b = *reinterpret_cast<const float4*>(resid + m * d + c);
+        v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+      }
+      *reinterpret_cast<float4*>(dx + m * d + c) = v;
+    }
+  }
+}
+void ln_mod_bwd_resid(cudaStream_t st, const float* dy, const float* xhat, const float* rstd, long long M, int d,
+                      const float* scale, long long vec_bstride, int rows_per_batch, const float* resid, float* dx) {
+  if (d % 128 == 0 && d <= 1024 && vec_bstride % 4 == 0 && al16f(dy) && al16f(xhat) && al16f(scale) && al16f(dx) &&
+      (resid == nullptr || al16f(resid))) {
+    ln_mod_bwd4_kernel<<<cdiv(M, 8), 256, 0, st>>>(dy, xhat, rstd, M, d, scale, vec_bstride, rows_per_batch, resid, dx);
+    F5B_POST_LAUNCH();
+    return;
+  }
+  if (resid != nullptr && resid != dx)
+    F5B_CHECK_CUDA(cudaMemcpyAsync(dx, resid, (size_t)M * d * 4, cudaMemcpyDeviceToDevice, st));
+  ln_mod_bwd_kernel<<<cdiv(M, 8), 256, 0, st>>>(dy, xhat, rstd, M, d, scale, vec_bstride, rows_per_batch, dx, resid ? 1 : 0);
+  F5B_POST_LAUNCH();
+}
 void ln_mod_bwd(cudaStream_t st, const float* dy, const float* xhat, const float* rstd, long long M, int d,
                 const float* scale, long long vec_bstride, int rows_per_batch, float* dx, bool accumulate) {
-  ln_mod_bwd_kernel<<<cdiv(M, 8), 256, 0, st>>>(dy, xhat, rstd, M, d, scale, vec_bstride, rows_per_batch, dx, accumulate ? 1 : 0);
-  F5B_POST_LAUNCH();
+  ln_mod_bwd_resid(st, dy, xhat, rstd, M, d, scale, vec_bstride, rows_per_batch, accumulate ? dx : nullptr, dx);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -402,6 +455,38 @@ rowscale4_kernel(const float4* __restrict__ x, const float* __restrict__ v, long
     a.x *= s.x; a.y *= s.y; a.z *= s.z; a.w *= s.w;
   }
   out[i] = a;
+}
+// out = base + v[b] * x   (the residual update x1 = x0 + gate * o in one pass instead of scale, copy, add)
+__global__ void __launch_bounds__(256)
+rowscale_add4_kernel(const float4* __restrict__ base, const float4* __restrict__ x, const float* __restrict__ v,
+                     long long vec_bstride, int rows_per_batch, int cols4, long long total4, float4* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total4) return;
+  const long long m = i / cols4;
+  const int c = (int)(i - m * cols4) * 4;
+  const long long b = m / rows_per_batch;
+  const float4 s = *reinterpret_cast<const float4*>(v + b * vec_bstride + c);
+  const float4 a = x[i], r = base[i];
+  out[i] = make_float4(fmaf(s.x, a.x, r.x), fmaf(s.y, a.y, r.y), fmaf(s.z, a.z, r.z), fmaf(s.w, a.w, r.w));
+}
+__global__ void __launch_bounds__(256)
+rowscale_add_kernel(const float* __restrict__ base, const float* __restrict__ x, const float* __restrict__ v,
+                    long long vec_bstride, int rows_per_batch, int cols, long long total, float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  const long long m = i / cols;
+  out[i] = fmaf(v[(m / rows_per_batch) * vec_bstride + (i - m * cols)], x[i], base[i]);
+}
+void rowscale_add(cudaStream_t st, const float* base, const float* x, const float* v, long long vec_bstride,
+                  int rows_per_batch, long long M, int cols, float* out) {
+  if (cols % 4 == 0 && vec_bstride % 4 == 0 && al16(base) && al16(x) && al16(out) && al16(v))
+    rowscale_add4_kernel<<<cdiv(M * (cols / 4), 256), 256, 0, st>>>(reinterpret_cast<const float4*>(base),
+                                                                   reinterpret_cast<const float4*>(x), v, vec_bstride,
+                                                                   rows_per_batch, cols / 4, M * (cols / 4),
+                                                                   reinterpret_cast<float4*>(out));
+  else
+    rowscale_add_kernel<<<cdiv(M * cols, 256), 256, 0, st>>>(base, x, v, vec_bstride, rows_per_batch, cols, M * cols, out);
+  F5B_POST_LAUNCH();
 }
 void rowscale(cudaStream_t st, const float* x, const float* v, long long vec_bstride, int rows_per_batch,
               const int* row_len, long long M, int cols, float* out) {

@@ -11,6 +11,11 @@ void sgemm_strided(cudaStream_t st, const float* A, long long sa0, long long sa1
 void sgemm_set_scratch(float* p, size_t floats);
 float* colsum_scratch(size_t* floats);  // the buffer handed to colsum_set_scratch (shared by the depthwise-conv wgrad)
 // out[b*out_bstride + j] = sum_{r in batch b} X[r,j] * (Y ? Y[r,j] : 1)
+// out = base + v[b(m), :] * x   and   dx = resid + LayerNorm-backward(dy)   (fused residual updates)
+void rowscale_add(cudaStream_t st, const float* base, const float* x, const float* v, long long vec_bstride,
+                  int rows_per_batch, long long M, int cols, float* out);
+void ln_mod_bwd_resid(cudaStream_t st, const float* dy, const float* xhat, const float* rstd, long long M, int d,
+                      const float* scale, long long vec_bstride, int rows_per_batch, const float* resid, float* dx);
 void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
                   long long out_bstride);
 // scratch for the two-level form (>= 128 * cols floats; per calling thread); null switches it off

@@ -919,6 +919,52 @@ void widen_bf16(cudaStream_t st, const void* src, long long n, float* dst) {
     widen_bf16_kernel<<<cdiv(n, 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(src), n, dst);
   F5B_POST_LAUNCH();
 }
+// One pass over an upstream gradient dY [R, C] (fp32) for everything its linear layer's backward needs from it:
+//   dst16 [R, C]   bf16 copy, the K-major A operand of the dgrad GEMM
+//   dstT  [C, ldT] bf16 transpose (columns >= R zero), the K-major A operand of the wgrad GEMM
+//   part  [row tiles, C] column sums of the 64-row tiles -> bias gradient (summed in tile order by colsum_final)
+// instead of a cast pass, a transpose pass and a column-sum pass that each read dY.  64 x 64 tiles, C % 64 == 0.
+__global__ void __launch_bounds__(256)
+prep_dy16_kernel(const float* __restrict__ src, long long R, int C, uint16_t* __restrict__ dst16,
+                 uint16_t* __restrict__ dstT, long long ldT, float* __restrict__ part) {
+  __shared__ float tile[64][65];  // [column][row]
+  const long long r0 = (long long)blockIdx.x * 64;
+  const int c0 = blockIdx.y * 64;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int k = ty; k < 64; k += 8) {
+    const long long r = r0 + k;
+    float2 v = make_float2(0.f, 0.f);
+    if (r < R) {
+      v = *reinterpret_cast<const float2*>(src + r * C + c0 + 2 * tx);
+      *reinterpret_cast<uint32_t*>(dst16 + r * C + c0 + 2 * tx) = (uint32_t)to16(v.x, 0) | ((uint32_t)to16(v.y, 0) << 16);
+    }
+    tile[2 * tx][k] = v.x;
+    tile[2 * tx + 1][k] = v.y;
+  }
+  __syncthreads();
+  for (int k = ty; k < 64; k += 8) {
+    const int c = c0 + k;
+    const float a = tile[k][2 * tx], b = tile[k][2 * tx + 1];
+    const long long r = r0 + 2 * tx;
+    if (r < ldT) *reinterpret_cast<uint32_t*>(dstT + (long long)c * ldT + r) = (uint32_t)to16(a, 0) | ((uint32_t)to16(b, 0) << 16);
+    float s = a + b;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(0xffffffffu, s, off);
+    if (tx == 0) part[(long long)blockIdx.x * C + c] = s;
+  }
+}
+// returns false (nothing done) when the shape does not fit the fused form
+bool prep_dy16(cudaStream_t st, const float* src, long long R, int C, void* dst16, void* dstT, long long ldT, float* part,
+               size_t part_floats, float* colsum_out) {
+  const long long tiles = (ldT + 63) / 64;
+  if (C % 64 != 0 || ldT % 2 != 0 || (size_t)tiles * C > part_floats || part == nullptr) return false;
+  prep_dy16_kernel<<<dim3((unsigned)tiles, C / 64), 256, 0, st>>>(src, R, C, reinterpret_cast<uint16_t*>(dst16),
+                                                                 reinterpret_cast<uint16_t*>(dstT), ldT, part);
+  F5B_POST_LAUNCH();
+  colsum_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(part, (int)tiles, C, colsum_out);
+  F5B_POST_LAUNCH();
+  return true;
+}
 void transpose_cast16(cudaStream_t st, const float* src, long long lds, long long R, int C, void* dst, long long ldd,
                       int fp16) {
   if (ldd % 2 == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {

@@ -11,6 +11,9 @@ void sgemm_strided(cudaStream_t st, const float* A, long long sa0, long long sa1
 void sgemm_set_scratch(float* p, size_t floats);
 float* colsum_scratch(size_t* floats);  // the buffer handed to colsum_set_scratch (shared by the depthwise-conv wgrad)
 // out[b*out_bstride + j] = sum_{r in batch b} X[r,j] * (Y ? Y[r,j] : 1)
+// dY [R, C] fp32 -> bf16 copy, bf16 transpose [C, ldT] and column sums in one pass (false: shape not supported)
+bool prep_dy16(cudaStream_t st, const float* src, long long R, int C, void* dst16, void* dstT, long long ldT, float* part,
+               size_t part_floats, float* colsum_out);
 // out = base + v[b(m), :] * x   and   dx = resid + LayerNorm-backward(dy)   (fused residual updates)
 void rowscale_add(cudaStream_t st, const float* base, const float* x, const float* v, long long vec_bstride,
                   int rows_per_batch, long long M, int cols, float* out);

@@ -96,8 +96,47 @@ gconv_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const
   }
   z[i] = acc;
 }
+// Depthwise form (groups == C, the ConvNeXt blocks' k = 7): a thread owns one channel of a 64-row slice of one batch
+// element and slides a register window down the rows -- every input is read once, coalesced over the channels, no
+// index division per element.  DIR = +1: forward (z = bias + sum_k x[t + k - pad] w[k], input rows >= len read as zero);
+// DIR = -1: data gradient (dx = sum_k dz[t - k + pad] w[k] for t < len, 0 beyond).
+template <int TAPS, int DIR>
+__global__ void __launch_bounds__(256)
+dwconv_slide_kernel(const float* __restrict__ in, const float* __restrict__ w, const float* __restrict__ bias, int rows,
+                    int C, const int* __restrict__ row_len, float* __restrict__ out) {
+  constexpr int PAD = TAPS / 2, SLICE = 64;
+  const int c = blockIdx.x * 256 + threadIdx.x, t0 = blockIdx.y * SLICE, b = blockIdx.z;
+  if (c >= C) return;
+  const int len = row_len ? row_len[b] : rows;
+  const int in_len = DIR > 0 ? len : rows;  // rows of the input that exist (dz is defined on every row)
+  float wk[TAPS], win[TAPS];
+#pragma unroll
+  for (int k = 0; k < TAPS; ++k) wk[k] = w[(long long)c * TAPS + (DIR > 0 ? k : TAPS - 1 - k)];
+  const float* ib = in + (long long)b * rows * C + c;
+  float* ob = out + (long long)b * rows * C + c;
+  auto ld = [&](int t) { return (t >= 0 && t < in_len) ? ib[(long long)t * C] : 0.0f; };
+#pragma unroll
+  for (int k = 0; k < TAPS - 1; ++k) win[k + 1] = ld(t0 + k - PAD);  // window holds rows t - PAD .. t + PAD
+  const float bv = (DIR > 0 && bias) ? bias[c] : 0.0f;
+  const int t1 = min(rows, t0 + SLICE);
+  for (int t = t0; t < t1; ++t) {
+#pragma unroll
+    for (int k = 0; k < TAPS - 1; ++k) win[k] = win[k + 1];
+    win[TAPS - 1] = ld(t + PAD);
+    float acc = bv;
+#pragma unroll
+    for (int k = 0; k < TAPS; ++k) acc = fmaf(win[k], wk[k], acc);
+    ob[(long long)t * C] = (DIR < 0 && t >= len) ? 0.0f : acc;
+  }
+}
+
 void gconv_fwd(cudaStream_t st, const float* x, const float* w, const float* bias, int batches, int rows, int C, int groups,
                int taps, const int* row_len, float* z) {
+  if (groups == C && taps == 7) {
+    dwconv_slide_kernel<7, 1><<<dim3(cdiv2(C, 256), cdiv2(rows, 64), batches), 256, 0, st>>>(x, w, bias, rows, C, row_len, z);
+    F5B_POST_LAUNCH();
+    return;
+  }
   const long long total = (long long)batches * rows * C;
   gconv_fwd_kernel<<<cdiv2(total, 256), 256, 0, st>>>(x, w, bias, rows, C, C / groups, taps, row_len, total, z);
   F5B_POST_LAUNCH();
@@ -126,6 +165,11 @@ gconv_dgrad_kernel(const float* __restrict__ dz, const float* __restrict__ w, in
 }
 void gconv_dgrad(cudaStream_t st, const float* dz, const float* w, int batches, int rows, int C, int groups, int taps,
                  const int* row_len, float* dx) {
+  if (groups == C && taps == 7) {
+    dwconv_slide_kernel<7, -1><<<dim3(cdiv2(C, 256), cdiv2(rows, 64), batches), 256, 0, st>>>(dz, w, nullptr, rows, C, row_len, dx);
+    F5B_POST_LAUNCH();
+    return;
+  }
   const long long total = (long long)batches * rows * C;
   gconv_dgrad_kernel<<<cdiv2(total, 256), 256, 0, st>>>(dz, w, rows, C, C / groups, taps, row_len, total, dx);
   F5B_POST_LAUNCH();

@@ -961,7 +961,9 @@ bool prep_dy16(cudaStream_t st, const float* src, long long R, int C, void* dst1
   prep_dy16_kernel<<<dim3((unsigned)tiles, C / 64), 256, 0, st>>>(src, R, C, reinterpret_cast<uint16_t*>(dst16),
                                                                  reinterpret_cast<uint16_t*>(dstT), ldT, part);
   F5B_POST_LAUNCH();
-  colsum_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(part, (int)tiles, C, colsum_out);
+  // the tile sums ([tiles, C], 600 x 3072 at C5 sizes) are added with the 16-byte, four-row-group kernel: the
+  // one-thread-per-column loop of colsum_final took 35 us here
+  colsum_seg4_kernel<<<dim3(cdiv(C, 256), 1), 256, 0, st>>>(part, nullptr, (int)tiles, (int)tiles, C, colsum_out, 0);
   F5B_POST_LAUNCH();
   return true;
 }

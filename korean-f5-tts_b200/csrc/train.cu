@@ -1,8 +1,10 @@
 // Backward kernels of the flow-matching training step (reference src/f5_tts/model/cfm.py:231-302 differentiated by
-// trainer.py:384 `accelerator.backward(loss)`), stage 1: everything needed to push the loss gradient through
-// proj_out, the final AdaLN and one DiTBlock (modules.py:683-697).  fp32 CUDA-core arithmetic: this is the parity
-// tier of the backward pass (checked against torch.autograd over the unmodified reference, tests/test_gpu_backward.py);
-// the tensor-core tier (dgrad / wgrad on tcgen05) is not built yet.  Deterministic: no atomics, fixed reduction order.
+// trainer.py:384 `accelerator.backward(loss)`): everything needed to push the loss gradient through proj_out, the final
+// AdaLN and a DiTBlock (modules.py:683-697) that is not a tensor-core contraction.  The fp32 CUDA-core GEMM / attention
+// kernels here are the parity tier of the backward pass (checked against torch.autograd over the unmodified reference,
+// tests/test_gpu_backward.py); in 16-bit mode the contractions run on tc_gemm / tc_attn / tc_attn_bwd and this file
+// supplies the staging (cast, transpose, prep_dy16), the reductions and the elementwise derivatives around them.
+// Deterministic: no atomics, fixed reduction order.
 #include "train.h"
 
 namespace f5b {

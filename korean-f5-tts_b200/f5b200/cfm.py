@@ -88,7 +88,7 @@ class CFM(nn.Module):
         """Flow-matching loss of one batch (cfm.py:231-302) -> (loss, cond, pred): the host draws (`_prepare_loss`), then
         phi, the infilling condition, the backbone evaluation and the masked MSE in one `f5b_cfm_loss` call.
         `draws` (keys frac_lengths, rand, x0, time, drop_audio_cond, drop_text) injects the random quantities (parity
-        tests).  The result carries no autograd graph; gradients come from `tail_gradients` (stage 1 of the backward)."""
+        tests).  The result carries no autograd graph; gradients come from `tail_gradients` (the backward pass)."""
         q = self._prepare_loss(inp, text, lens, draws)
         x1, dev = q["x1"], q["dev"]
         loss = torch.empty((1,), device=dev, dtype=torch.float32)

@@ -229,7 +229,7 @@ void copy_out(void* dst, const void* src, size_t bytes, int mem, cudaStream_t st
 // Device properties are queried ONCE per device (cudaGetDeviceProperties costs milliseconds; every f5b_op_* entry and
 // every optimiser step used to pay it twice) and the kernel attributes are set once per device as well.
 struct DeviceInfo {
-  bool checked = false, kernels_ready = false;
+  std::atomic<bool> checked{false}, kernels_ready{false};  // read on the lock-free fast path, written under g_dev_mu
   int major = 0, minor = 0, sm_count = 0;
   std::string name;
 };
@@ -237,7 +237,8 @@ static std::mutex g_dev_mu;
 static DeviceInfo g_dev[64];
 
 static DeviceInfo& device_check_throw(int device) {
-  if (device >= 0 && device < 64 && g_dev[device].checked && g_dev[device].major == 10) {  // fast path (written once)
+  if (device >= 0 && device < 64 && g_dev[device].checked.load(std::memory_order_acquire) &&
+      g_dev[device].major == 10) {  // fast path: the fields are written once, before `checked` is released
     F5B_CHECK_CUDA(cudaSetDevice(device));
     return g_dev[device];
   }
@@ -261,7 +262,7 @@ static DeviceInfo& device_check_throw(int device) {
     d.minor = p.minor;
     d.sm_count = p.multiProcessorCount;
     d.name = p.name;
-    d.checked = true;
+    d.checked.store(true, std::memory_order_release);
   }
   if (d.major != 10) {
     set_error(std::string("device '") + d.name + "' is sm_" + std::to_string(d.major) + std::to_string(d.minor) +
@@ -285,7 +286,7 @@ DeviceCtx open_device(int device, int mode) {
       tc_attn_bwd_init_kernels();
       tc_gemm_init_kernels();
       simt_init_kernels();
-      d.kernels_ready = true;
+      d.kernels_ready.store(true, std::memory_order_release);
     }
   }
   return c;

@@ -204,6 +204,48 @@ float* colsum_scratch(size_t* floats) {
   *floats = g_colsum_scratch_floats;
   return g_colsum_scratch;
 }
+// Both AdaLN sums of one upstream gradient in one pass: out_xy[b, j] = sum_r X Y, out_x[b, j] = sum_r X (per batch
+// element) -- d scale and d shift of a modulated LayerNorm read the same X; the pair of colsum_batch calls read it twice.
+__global__ void __launch_bounds__(256)
+colsum_pair4_kernel(const float* __restrict__ X, const float* __restrict__ Y, int seg_rows, int cols,
+                    float* __restrict__ out_xy, float* __restrict__ out_x, long long out_sstride) {
+  __shared__ float4 red[2][4][64];
+  const int q = threadIdx.x & 63, g = threadIdx.x >> 6, s = blockIdx.y;
+  const int c = (blockIdx.x * 64 + q) * 4;
+  const long long r0 = (long long)s * seg_rows, r1 = r0 + seg_rows;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+  if (c < cols) {
+    for (long long r = r0 + g; r < r1; r += 4) {
+      const float4 x = *reinterpret_cast<const float4*>(X + r * cols + c);
+      const float4 y = *reinterpret_cast<const float4*>(Y + r * cols + c);
+      a.x = fmaf(x.x, y.x, a.x); a.y = fmaf(x.y, y.y, a.y); a.z = fmaf(x.z, y.z, a.z); a.w = fmaf(x.w, y.w, a.w);
+      b.x += x.x; b.y += x.y; b.z += x.z; b.w += x.w;
+    }
+  }
+  red[0][g][q] = a;
+  red[1][g][q] = b;
+  __syncthreads();
+  if (g < 2 && c < cols) {  // group 0 finishes the X Y sums, group 1 the X sums: the four row groups in order
+    float4 t = red[g][0][q];
+#pragma unroll
+    for (int k = 1; k < 4; ++k) {
+      t.x += red[g][k][q].x; t.y += red[g][k][q].y; t.z += red[g][k][q].z; t.w += red[g][k][q].w;
+    }
+    float* o = (g == 0 ? out_xy : out_x) + (long long)s * out_sstride + c;
+    o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+  }
+}
+void colsum_batch_pair(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols,
+                       float* out_xy, float* out_x, long long out_bstride) {
+  if (cols % 4 == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0 && (reinterpret_cast<uintptr_t>(Y) & 15) == 0) {
+    colsum_pair4_kernel<<<dim3(cdiv(cols, 256), batches), 256, 0, st>>>(X, Y, rows_per_batch, cols, out_xy, out_x,
+                                                                       out_bstride);
+    F5B_POST_LAUNCH();
+    return;
+  }
+  colsum_batch(st, X, Y, batches, rows_per_batch, cols, out_xy, out_bstride);
+  colsum_batch(st, X, nullptr, batches, rows_per_batch, cols, out_x, out_bstride);
+}
 void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
                   long long out_bstride) {
   constexpr int kChunks = 128;

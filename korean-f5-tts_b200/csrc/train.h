@@ -19,6 +19,8 @@ void rowscale_add(cudaStream_t st, const float* base, const float* x, const floa
                   int rows_per_batch, long long M, int cols, float* out);
 void ln_mod_bwd_resid(cudaStream_t st, const float* dy, const float* xhat, const float* rstd, long long M, int d,
                       const float* scale, long long vec_bstride, int rows_per_batch, const float* resid, float* dx);
+void colsum_batch_pair(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols,
+                       float* out_xy, float* out_x, long long out_bstride);
 void colsum_batch(cudaStream_t st, const float* X, const float* Y, int batches, int rows_per_batch, int cols, float* out,
                   long long out_bstride);
 // scratch for the two-level form (>= 128 * cols floats; per calling thread); null switches it off
